@@ -1,0 +1,111 @@
+"""The oracle against fixtures produced by the reference itself (tests/golden/gen_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.mark.parametrize("bits,gs,sym", [(8, -1, True), (4, -1, True), (4, 128, True), (4, 128, False),
+                                         (4, -1, False), (8, 128, False), (8, -1, False), (2, 128, False)])
+def test_quant_minmax_matches_reference(bits, gs, sym):
+    d = np.load(os.path.join(G, "quant_minmax.npz"))
+    key = f"b{bits}_g{gs}_{'sym' if sym else 'asym'}"
+    q, s, z = O.quant_minmax(d["x"], bits, gs, sym)
+    assert np.array_equal(s, d[key + "_s"])
+    assert np.array_equal(z, d[key + "_z"])
+    assert np.array_equal(q, d[key + "_q"])
+    fq = O.fake_quant(d["x"], bits, gs, sym)
+    assert np.array_equal(fq.view(np.uint16), d[key + "_fq"].view(np.uint16))
+
+
+@pytest.mark.parametrize("n", [64, 2048, 1408, 2560, 1792, 5632, 96])
+def test_hadamard_matches_reference(n):
+    d = np.load(os.path.join(G, "hadamard.npz"))
+    _, k = O.get_hadK(n)
+    assert k == int(d[f"k{n}"])
+    y = O.hadamard(d[f"x{n}"])
+    # the reference divides by a float32 sqrt(n) (hadamard_utils.py:83) -> 1e-7 relative
+    np.testing.assert_allclose(y, d[f"y{n}"], rtol=2e-7, atol=1e-9)
+    # orthogonality: H H^T = I  -> applying twice with the transpose restores x for K==1
+    if k == 1:
+        np.testing.assert_allclose(O.hadamard(y), d[f"x{n}"], atol=1e-12)
+
+
+def test_hadk_selection_order():
+    # hadamard_utils.py:39-50: 28 is tested before 40, 40 before 20
+    assert O.get_hadK(14336)[1] == 28
+    assert O.get_hadK(2560)[1] == 40
+    assert O.get_hadK(20480)[1] == 40
+    assert O.get_hadK(1408)[1] == 176
+    assert O.get_hadK(5632)[1] == 176
+    assert O.get_hadK(4096)[1] == 1
+
+
+@pytest.mark.parametrize("bits", [8, 4, 2])
+@pytest.mark.parametrize("sym", [True, False])
+def test_pack_weightonly_matches_reference(bits, sym):
+    d = np.load(os.path.join(G, "pack.npz"))
+    key = f"wonly_b{bits}_{'sym' if sym else 'asym'}"
+    q, p = d[key + "_q"], d[key + "_p"]
+    assert np.array_equal(O.pack_weightonly_ref(q, bits, sym), p)
+    assert np.array_equal(O.unpack_weightonly_ref(p, bits, sym, *q.shape), q)
+
+
+@pytest.mark.parametrize("bits", [8, 4])
+def test_pack_wxax_matches_reference(bits):
+    d = np.load(os.path.join(G, "pack.npz"))
+    for t in ("a", "w"):
+        q, p = d[f"wxax_b{bits}_{t}"], d[f"wxax_b{bits}_p{t}"]
+        assert np.array_equal(O.pack_wxax(q, bits), p)
+        assert np.array_equal(O.unpack_wxax(p, bits), q)
+
+
+@pytest.mark.parametrize("sym", [True, False])
+def test_permute_scale_matches_reference(sym):
+    d = np.load(os.path.join(G, "pack.npz"))
+    k = "sym" if sym else "asym"
+    s = d[f"scale_{k}_in"]
+    out = O.permute_scale(s[..., 0], None if sym else s[..., 1], sym)
+    ref = d[f"scale_{k}_out"]
+    assert np.array_equal(out.reshape(ref.shape), ref)
+
+
+def test_gemm_wxax_int_exact_and_order():
+    rng = np.random.default_rng(0)
+    A = (rng.random((40, 256)) * 2 - 1).astype(np.float16)
+    W = (rng.random((48, 256)) * 2 - 1).astype(np.float16)
+    for bits, gs in ((8, -1), (4, -1), (4, 128)):
+        qa, sa = O.quant_act(A, bits, gs)
+        qw, sw, _ = O.quant_weight(W, bits, gs, True)
+        acc, out = O.gemm_wxax(qa, sa, qw, sw, gs)
+        g = 256 if gs == -1 else gs
+        for i in range(256 // g):
+            ref = qa[:, i * g:(i + 1) * g].astype(np.int64) @ qw[:, i * g:(i + 1) * g].astype(np.int64).T
+            assert np.array_equal(acc[i], ref)
+        # close to the un-quantized product for 8 bit
+        if bits == 8:
+            full = A.astype(np.float64) @ W.astype(np.float64).T
+            assert np.abs(out.astype(np.float64) - full).max() < 0.25
+
+
+def test_permute_and_combine_roundtrip():
+    rng = np.random.default_rng(1)
+    T, k, E, H = 37, 4, 12, 16
+    ids = np.stack([rng.permutation(E)[:k] for _ in range(T)]).astype(np.int32)
+    offs, src, slot = O.permute(ids, E)
+    assert offs[-1] == T * k
+    # rows of expert e are contiguous and keep token order (stable)
+    flat = ids.reshape(-1)
+    for e in range(E):
+        seg = src[offs[e]:offs[e + 1]]
+        assert np.all(np.diff(seg) >= 0)
+        assert np.all([e in ids[t] for t in seg])
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    w = np.full((T, k), 0.25, np.float32)
+    out = O.combine(x[src], slot, w)
+    np.testing.assert_allclose(out.astype(np.float32), x.astype(np.float32), atol=2e-3)
+    assert flat[np.argsort(flat, kind="stable")][slot.reshape(-1)].tolist() == flat.tolist()
