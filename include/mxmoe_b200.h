@@ -1,0 +1,158 @@
+/* mxmoe_b200 — C-ABI of the B200-native mixed-precision MoE GroupGEMM path.
+ *
+ * This header is the drop-in boundary for the hot path that the reference drives from
+ * run_mxmoe_gg.py.  Every entry point is `extern "C"`, takes plain pointers / sizes / a
+ * cudaStream_t passed as void*, returns 0 on success or a negative MXB_E* code, never throws and
+ * never calls exit().  mxb_last_error() returns a thread-local message for the last failure.
+ * All data pointers are DEVICE pointers unless a parameter is documented as host.
+ *
+ * Reference interfaces replaced (paths relative to the reference repository):
+ *   mxb_group_gemm            mxmoe::FuncType, mxmoe/kernels/src/include/registry.cuh:28-39
+ *                             (generated launcher: mxmoe/kernels/kernel_sketch.py:82-145)
+ *   mxb_group_gemm_reflayout  the same FuncType argument list, verbatim (SoA of device arrays)
+ *   mxb_permute               gg_permute_inp, mxmoe/kernels/src/ref_bind.cu:47-64
+ *   mxb_quant_act             quant_inp_act / quant_act_kernel call site, ref_bind.cu:434-592
+ *   mxb_silu_mul_quant        silu_mul_then_quant, ref_bind.cu:595-757 (+ online Hadamard,
+ *                             mxmoe/quant/rotation.py:403-421, hadamard_utils.py:96-105)
+ *   mxb_combine               gg_unpermute_out (empty in the reference, ref_bind.cu:66); routing
+ *                             weights as mxmoe/quant/moe_tracer.py:79-86
+ *   mxb_quant_pack_weight     quant_weight kernel + host packers, quantize.cuh:218-475
+ *   mxb_repack_from_ref       reads the reference's packed layouts (quantize.cuh:318-475)
+ *   mxb_select_tiles          get_possible_tile_list / get_best_tile_configs,
+ *                             mxmoe/kernels/tile_config.py:330-610, mxmoe/quant/bits_solver.py:425-515
+ */
+#ifndef MXMOE_B200_H_
+#define MXMOE_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MXB_OK 0
+#define MXB_EINVAL (-1)     /* bad argument / unsupported qconfig (the reference throws std::runtime_error) */
+#define MXB_ECUDA (-2)      /* a CUDA runtime/driver call failed (the reference prints and exit()s) */
+#define MXB_ENOMEM (-3)
+#define MXB_EUNSUPPORTED (-4) /* device is not sm_100 */
+
+typedef struct mxb_context* mxb_handle_t;
+
+/* One GroupGEMM problem: C[M,N] = A[M,K] * B[N,K]^T in the precision named by (w_bits, a_bits, gsize, sym).
+ * Mirrors one entry of the reference's (ptr_As[i], ptr_Bs[i], ptr_scale_a[i], ptr_scale_b[i], ptr_Cs[i],
+ * problem_sizes[i], qbits_list[i]) SoA, registry.cuh:28-39 + quantize.cuh:14-25 (QParams).
+ *
+ * Operand formats ("native" layouts, produced by mxb_quant_pack_weight / mxb_repack_from_ref / mxb_quant_act):
+ *   fp16      (w16 a16) : A fp16 [M,K] (row pitch lda elements), B fp16 [N,K]
+ *   w8a8      sym g-1   : A int8 [M,K], B int8 [N,K], scale_a fp16 [M], scale_b fp16 [N]
+ *   w4a4      sym g-1   : A int8 containers holding values in [-7,7] [M,K]; B 4-bit [N,K/2] bytes, inside
+ *                         every 32-k block byte j holds k=j in the low and k=j+16 in the high nibble
+ *                         (two's complement); scale_a fp16 [M], scale_b fp16 [N]
+ *   w4a4      sym g128  : as above; scale_a fp16 [M, K/128], scale_b fp16 [K/128, N]
+ *   wNa16     (N=4,8)   : A fp16 [M,K]; B unsigned codes (sym: q + 2^(N-1)-1), 4-bit: [N,K/2] bytes with
+ *                         the nibble order k = 0,2,4,6,1,3,5,7 inside every 32-bit word; 8-bit: [N,K];
+ *                         scale_b fp16 [K/g, N] (sym) or [K/g, N, 2] = (scale, zero-offset) (asym),
+ *                         the group-major layout of permute_scale (quantize.cuh:299-315)
+ * C is fp16 [M,N] with row pitch ldc elements.
+ *
+ * Device-resident M (no host sync after routing): when m_range is non-NULL it points at two consecutive
+ * int32 on the DEVICE, {row_begin, row_end} (e.g. expert_offsets + e).  A, scale_a and C are then the bases
+ * of buffers shared by all problems and this problem owns rows [row_begin,row_end); M is the row capacity
+ * of those buffers.
+ */
+typedef struct MxbProblem {
+  const void* A;
+  const void* B;
+  const void* scale_a;
+  const void* scale_b;
+  void* C;
+  const int32_t* m_range;
+  int64_t lda; /* elements of A's storage type per row; 0 = dense */
+  int64_t ldc; /* fp16 elements per row of C; 0 = N */
+  int32_t M, N, K;
+  int32_t a_bits, w_bits, gsize, sym; /* gsize -1 = per-channel/per-token */
+  int32_t tile_n;                     /* 0 = let the selector choose; else 64/128/256 */
+  int32_t reserved;
+} MxbProblem;
+
+/* Per-expert activation quantization parameters for mxb_quant_act / mxb_silu_mul_quant
+ * (the reference's qparams_per_exp tuples, ref_bind.cu:321,365). */
+typedef struct MxbActQ {
+  int32_t a_bits; /* 16 = keep fp16, 8, 4 (stored in int8 containers) */
+  int32_t gsize;  /* -1 or 128 */
+} MxbActQ;
+
+typedef struct MxbTileChoice {
+  int32_t tile_m, tile_n, tile_k, stages;
+  int32_t path;       /* 0 = tcgen05 persistent GroupGEMM, 1 = HBM-streaming w4a16 */
+  float est_us;       /* cost-model estimate for this problem alone */
+} MxbTileChoice;
+
+/* ---- lifetime ---- */
+int mxb_create(int device, mxb_handle_t* out);
+int mxb_destroy(mxb_handle_t h);
+const char* mxb_last_error(void);
+int mxb_sm_count(mxb_handle_t h);
+const char* mxb_version(void);
+
+/* ---- piece (3)+(4): one launch over a mixed-precision problem list ---- */
+/* `problems` is a HOST array.  Plans (tile tables, tensor maps) are cached in the handle keyed by its content. */
+int mxb_group_gemm(mxb_handle_t h, const MxbProblem* problems, int problem_count, void* stream);
+/* Same launch, but integer problems also dump their int32 accumulators (after removing the internal x16 of
+ * the 4-bit path) to acc_out[i] (device int32 [M,N], may be NULL per problem).  For the bit-exact check. */
+int mxb_group_gemm_debug_acc(mxb_handle_t h, const MxbProblem* problems, int problem_count,
+                             int32_t* const* acc_out, void* stream);
+/* Verbatim FuncType argument list (registry.cuh:28-39): device SoA arrays plus host copies of sizes/QParams.
+ * sizes are 3x uint32 (dim3: M,N,K); qparams are {int a_bits; int w_bits; int gsize; bool sym} = 16 bytes
+ * (quantize.cuh:14-25).  Operands must be in the native layouts above.  Uses the handle's own stream 0
+ * semantics like the reference when stream == NULL. */
+int mxb_group_gemm_reflayout(mxb_handle_t h, void** ptr_As, void** ptr_Bs, void** ptr_scale_a, void** ptr_scale_b,
+                             void** ptr_Cs, void** ptr_Ds, int64_t* ldas, int64_t* ldbs, int64_t* ldcs,
+                             int64_t* ldds, const void* dev_problem_sizes, const void* host_problem_sizes,
+                             const void* dev_qparams, const void* host_qparams, int problem_count, void* stream);
+
+/* ---- piece (1): token -> expert permute ---- */
+/* topk_ids int32 [T,k] with values in [0,E).  Outputs: expert_offsets int32 [E+1]; src_row int32 [T*k]
+ * (source token of every sorted slot, stable in (token, j) order); slot_of int32 [T,k] (sorted slot of (t,j)). */
+int mxb_permute(mxb_handle_t h, const int32_t* topk_ids, int T, int k, int E, int32_t* expert_offsets,
+                int32_t* src_row, int32_t* slot_of, void* stream);
+
+/* ---- piece (2): per-token activation quantization (+ optional Hadamard) ---- */
+/* x fp16 [T,H] gathered through src_row (NULL = identity, rows = n_rows) into sorted order; expert e owns
+ * rows [expert_offsets[e], expert_offsets[e+1]) and is quantized by actq[e] (HOST array, E entries).
+ * out_q8 int8 [rows,H] receives 8/4-bit rows, out_f16 fp16 [rows,H] receives a_bits==16 rows (either may be
+ * NULL if unused), scales fp16 [rows, H/128 if any gsize==128 else 1].  hadamard != 0 applies the online
+ * Hadamard rotation of hadamard_utils.py:96-105 to every row before quantization. */
+int mxb_quant_act(mxb_handle_t h, const void* x, int H, const int32_t* src_row, int n_rows,
+                  const int32_t* expert_offsets, const MxbActQ* actq, int E, int hadamard, void* out_q8,
+                  void* out_f16, void* scales, int scale_cols, void* stream);
+/* gate_up fp16 [rows, 2I] (gate in the first I columns) -> h = silu(gate)*up -> optional Hadamard over I ->
+ * per-token quantization as above into [rows, I] buffers. */
+int mxb_silu_mul_quant(mxb_handle_t h, const void* gate_up, int I, int n_rows, const int32_t* expert_offsets,
+                       const MxbActQ* actq, int E, int hadamard, void* out_q8, void* out_f16, void* scales,
+                       int scale_cols, void* stream);
+
+/* ---- piece (5): gather + top-k weighted combine ---- */
+/* out[t] = fp16( sum_j topk_w[t,j] * down_out[slot_of[t,j]] (+ shared_out[t]) ), fp32 accumulation in j order. */
+int mxb_combine(mxb_handle_t h, const void* down_out, int H, const int32_t* slot_of, const float* topk_w, int T,
+                int k, const void* shared_out, void* out, void* stream);
+
+/* ---- offline weight path ---- */
+/* W fp16 [N,K] -> native packed weights + scales for (w_bits, a_bits, gsize, sym); numerics of
+ * quant_weight (quantize.cuh:218-279).  packed/scales sizes: see mxb_packed_bytes / mxb_scale_elems. */
+int mxb_quant_pack_weight(mxb_handle_t h, const void* W, int N, int K, int w_bits, int a_bits, int gsize, int sym,
+                          void* packed, void* scales, void* stream);
+/* Reference-layout packed weights (pack_wxax when a_bits<16, permute_weight+pack_weightonly when a_bits==16)
+ * -> native layout.  Scales already share the reference's permute_scale layout and need no conversion. */
+int mxb_repack_from_ref(mxb_handle_t h, const void* ref_packed, int N, int K, int w_bits, int a_bits, int sym,
+                        void* packed, void* stream);
+int64_t mxb_packed_bytes(int N, int K, int w_bits);
+int64_t mxb_scale_elems(int N, int K, int w_bits, int a_bits, int gsize, int sym);
+
+/* ---- Blackwell tile selector / cost model ---- */
+int mxb_select_tiles(mxb_handle_t h, const MxbProblem* problems, int problem_count, MxbTileChoice* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MXMOE_B200_H_ */

@@ -1,0 +1,68 @@
+// Device-side problem descriptor shared between the host planner (api.cu) and the persistent
+// grouped-GEMM kernel (gg_kernel.cu).
+//
+// Replaces the reference's SoA of device arrays + QParams + host-computed tile prefix
+// (mxmoe/kernels/src/include/registry.cuh:28-39, quantize.cuh:14-25, kernel_sketch.py:87-104):
+// one AoS record per problem that also carries the two TMA tensor maps; the tile prefix sum is
+// computed on the device by every CTA so that M may live in device memory (m_range).
+#pragma once
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace mxb {
+
+enum MmaKind : int32_t { MMA_F16 = 0, MMA_I8 = 1 };
+enum ConvMode : int32_t {
+  CONV_NONE = 0,
+  CONV_W4_I8 = 1,   // 4-bit two's complement weights -> int8 x16 (nibble split), w4a4
+  CONV_W4_F16 = 2,  // 4-bit unsigned codes -> fp16 (LOP3 magic) * scale + zp, w4a16
+  CONV_W8_F16 = 3,  // 8-bit unsigned codes -> fp16, w8a16
+};
+enum EpiMode : int32_t {
+  EPI_F32 = 0,        // fp32 accumulator -> fp16
+  EPI_INT_ROWCOL = 1, // int32 accumulator * half(sa[m]*sb[n]) (mm_tile.cuh:472-496)
+  EPI_INT_GROUP = 2,  // per-128-K-group: out += float(acc_g) * half(sa[m,g]*sb[g,n]) (cta_gemm.cuh:580-602)
+};
+
+struct alignas(128) DevProblem {
+  CUtensorMap tmA;
+  CUtensorMap tmB;
+  const __half* scale_a;
+  const __half* scale_b;
+  __half* C;
+  int32_t* acc_out;
+  const int32_t* m_range;
+  int64_t ldc;
+  int32_t M, N, K;
+  int32_t mma_kind, conv, epi;
+  int32_t acc_shift;
+  int32_t bn;       // tile N (UMMA N), multiple of 16, <= 256 (<= 128 when conv != NONE)
+  int32_t n_tiles;  // ceil(N / bn)
+  int32_t kblocks;  // number of 128-byte K slabs of the MMA operand
+  int32_t a_kstep;  // tensor-map coordinate step per k-block (elements of the map's dtype)
+  int32_t b_kstep;
+  uint32_t tx_bytes;  // bytes TMA delivers per stage (A box + B box)
+  uint32_t idesc;
+  int32_t gsize, sym;
+  int32_t scale_a_ld;  // fp16 elements per row of scale_a (1 or K/gsize)
+  int32_t kb_per_group; // k-blocks per quantization group (EPI_INT_GROUP / grouped W-only)
+};
+static_assert(sizeof(DevProblem) == 384, "DevProblem layout");
+
+constexpr int GG_MAXP = 256;       // problems per launch (host splits longer lists)
+constexpr int GG_THREADS = 384;    // 12 warps: TMA, MMA, TMEM-alloc, spare, 4 epilogue, 4 converter
+constexpr int GG_BM = 128;
+constexpr int GG_STAGES = 4;
+constexpr int GG_A_BYTES = 128 * 128;   // 128 rows x 128 B
+constexpr int GG_B_BYTES = 256 * 128;   // up to 256 rows x 128 B
+constexpr int GG_STAGE_BYTES = GG_A_BYTES + GG_B_BYTES;
+constexpr int GG_PACKED_OFF = 128 * 128;  // packed staging inside the B region when conv != NONE
+constexpr int GG_EPI_STAGE_BYTES = 4 * 32 * 64;
+constexpr int GG_SMEM_BYTES = 1024 /*align slack*/ + GG_STAGES * GG_STAGE_BYTES + GG_EPI_STAGE_BYTES + 256 /*barriers*/ +
+                              (3 * GG_MAXP + 4) * 4;
+
+void gg_launch(const DevProblem* probs, int P, int grid, cudaStream_t stream);
+int gg_configure();  // cudaFuncSetAttribute(max dynamic smem); returns cudaError_t as int
+
+}  // namespace mxb

@@ -1,0 +1,502 @@
+// Pieces (1), (2) and (5) of the hot path plus the offline weight quantize/pack kernels.
+// All of them are HBM-bound byte/short kernels: 16-byte vector accesses, one warp per token row,
+// grids sized from the row count; no tensor cores except the K x K Hadamard factor (hadamard.cu).
+//
+// Reference semantics restated here (paths relative to the reference repo):
+//   permute           stable sort of flattened expert ids, ref_bind.cu:47-64, :449-453
+//   per-token quant   quant_minmax (mxmoe/quant/quant.py:40-84) in fp16 arithmetic, sym, with the
+//                     scale==0 -> 1 guard of quantize.cuh:256; call sites ref_bind.cu:531-544, 701-716
+//   silu*mul          HF act_fn(gate)*up in fp16 tensors (silu in fp32, rounded to fp16, product rounded)
+//   combine           routing-weighted sum, weights as moe_tracer.py:79-86 (absent in ref_bind.cu:66)
+//   quant_weight      quantize.cuh:218-279
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "moe_ops.cuh"
+
+namespace mxb {
+
+// ============================================================================ permute
+namespace {
+constexpr int PERM_THREADS = 256;
+constexpr int PERM_ITEMS = 8;
+constexpr int PERM_CHUNK = PERM_THREADS * PERM_ITEMS;
+
+// ws layout: [0] ticket, [1..1+nblk*E) block_hist -> turned into exclusive per-expert block bases
+__global__ void __launch_bounds__(PERM_THREADS) permute_hist_kernel(const int32_t* __restrict__ ids, int n, int E,
+                                                                     int32_t* __restrict__ ws,
+                                                                     int32_t* __restrict__ expert_offsets) {
+  extern __shared__ int32_t sh[];  // E ints (+1 flag)
+  const int nblk = gridDim.x, b = blockIdx.x;
+  for (int e = threadIdx.x; e < E; e += PERM_THREADS) sh[e] = 0;
+  __syncthreads();
+  const int base = b * PERM_CHUNK;
+#pragma unroll
+  for (int it = 0; it < PERM_ITEMS; ++it) {
+    int i = base + it * PERM_THREADS + threadIdx.x;
+    if (i < n) {
+      int e = ids[i];
+      if (e >= 0 && e < E) atomicAdd(&sh[e], 1);
+    }
+  }
+  __syncthreads();
+  int32_t* hist = ws + 1;
+  for (int e = threadIdx.x; e < E; e += PERM_THREADS) hist[b * E + e] = sh[e];
+  __threadfence();
+  __syncthreads();
+  __shared__ int last;
+  if (threadIdx.x == 0) last = (atomicAdd(&ws[0], 1) == nblk - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // last block: per expert, exclusive scan over blocks; then scan totals over experts
+  for (int e = threadIdx.x; e < E; e += PERM_THREADS) {
+    int run = 0;
+    for (int bb = 0; bb < nblk; ++bb) {
+      int c = hist[bb * E + e];
+      hist[bb * E + e] = run;
+      run += c;
+    }
+    sh[e] = run;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {  // warp scan of totals, 32 at a time
+    int carry = 0;
+    const int lane = threadIdx.x;
+    if (lane == 0) expert_offsets[0] = 0;
+    for (int b0 = 0; b0 < E; b0 += 32) {
+      int idx = b0 + lane;
+      int v = idx < E ? sh[idx] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+      }
+      if (idx < E) expert_offsets[idx + 1] = v + carry;
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+    if (lane == 0) ws[0] = 0;  // re-arm the ticket for the next call
+  }
+}
+
+__global__ void __launch_bounds__(PERM_THREADS) permute_scatter_kernel(const int32_t* __restrict__ ids, int n, int k, int E,
+                                                                        const int32_t* __restrict__ ws,
+                                                                        const int32_t* __restrict__ expert_offsets,
+                                                                        int32_t* __restrict__ src_row,
+                                                                        int32_t* __restrict__ slot_of) {
+  extern __shared__ int32_t sh[];
+  int32_t* run = sh;            // [E] running count inside this block
+  int32_t* wcnt = sh + E;       // [8][E] per-warp counts of the current round
+  const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int32_t* base_tab = ws + 1 + b * E;
+  for (int e = threadIdx.x; e < E; e += PERM_THREADS) run[e] = expert_offsets[e] + base_tab[e];
+  const int base = b * PERM_CHUNK;
+  for (int it = 0; it < PERM_ITEMS; ++it) {
+    for (int j = threadIdx.x; j < 8 * E; j += PERM_THREADS) wcnt[j] = 0;
+    __syncthreads();
+    const int i = base + it * PERM_THREADS + threadIdx.x;
+    int e = -1;
+    if (i < n) {
+      e = ids[i];
+      if (e < 0 || e >= E) e = -1;
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, e);
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    if (e >= 0 && rank == 0) wcnt[warp * E + e] = __popc(peers);
+    __syncthreads();
+    if (e >= 0) {
+      int off = run[e] + rank;
+      for (int w2 = 0; w2 < warp; ++w2) off += wcnt[w2 * E + e];
+      slot_of[i] = off;
+      src_row[off] = i / k;
+    }
+    __syncthreads();
+    for (int e2 = threadIdx.x; e2 < E; e2 += PERM_THREADS) {
+      int s = 0;
+#pragma unroll
+      for (int w2 = 0; w2 < 8; ++w2) s += wcnt[w2 * E + e2];
+      run[e2] += s;
+    }
+    __syncthreads();
+  }
+}
+}  // namespace
+
+size_t permute_ws_bytes(int n, int E) {
+  int nblk = (n + PERM_CHUNK - 1) / PERM_CHUNK;
+  return sizeof(int32_t) * (1 + static_cast<size_t>(nblk) * E);
+}
+
+cudaError_t permute_launch(const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
+                           int32_t* slot_of, int32_t* ws, cudaStream_t st) {
+  const int n = T * k;
+  const int nblk = (n + PERM_CHUNK - 1) / PERM_CHUNK;
+  if (nblk == 0) {
+    return cudaMemsetAsync(expert_offsets, 0, sizeof(int32_t) * (E + 1), st);
+  }
+  permute_hist_kernel<<<nblk, PERM_THREADS, sizeof(int32_t) * (E + 1), st>>>(ids, n, E, ws, expert_offsets);
+  permute_scatter_kernel<<<nblk, PERM_THREADS, sizeof(int32_t) * 9 * E, st>>>(ids, n, k, E, ws, expert_offsets, src_row,
+                                                                              slot_of);
+  return cudaGetLastError();
+}
+
+// ============================================================================ per-token quantization
+namespace {
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float half_warp_max(float v) {  // reduce inside each group of 16 lanes
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// torch-CPU fp16 semantics: every op computes in fp32 and rounds to fp16 (quant.py:66-82 on a half tensor)
+__device__ __forceinline__ float h_round(float x) { return __half2float(__float2half_rn(x)); }
+__device__ __forceinline__ float silu_mul_h(__half g, __half u) {
+  float gf = __half2float(g);
+  float s = h_round(__fdiv_rn(gf, 1.f + expf(-gf)));
+  return h_round(s * __half2float(u));
+}
+
+template <bool SILU>
+__device__ __forceinline__ void load8(const __half* __restrict__ row, int H, int idx8, float (&x)[8]) {
+  if (SILU) {
+    uint4 g = *reinterpret_cast<const uint4*>(row + idx8 * 8);
+    uint4 u = *reinterpret_cast<const uint4*>(row + H + idx8 * 8);
+    const __half* gh = reinterpret_cast<const __half*>(&g);
+    const __half* uh = reinterpret_cast<const __half*>(&u);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] = silu_mul_h(gh[j], uh[j]);
+  } else {
+    uint4 v = *reinterpret_cast<const uint4*>(row + idx8 * 8);
+    const __half* vh = reinterpret_cast<const __half*>(&v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] = __half2float(vh[j]);
+  }
+}
+
+__device__ __forceinline__ int find_expert(const int32_t* __restrict__ offs, int E, int row) {
+  int lo = 0, hi = E;  // largest e with offs[e] <= row
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (offs[mid] <= row) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// One warp per output row.  SILU=false: x row gathered through src_row; SILU=true: row = [gate | up].
+template <bool SILU>
+__global__ void __launch_bounds__(256) quant_rows_kernel(const __half* __restrict__ x, int H, int64_t in_pitch,
+                                                          const int32_t* __restrict__ src_row, int n_rows,
+                                                          const int32_t* __restrict__ expert_offsets,
+                                                          const int2* __restrict__ actq, int E, int8_t* __restrict__ out_q8,
+                                                          __half* __restrict__ out_f16, __half* __restrict__ scales,
+                                                          int scale_cols) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= n_rows) return;
+  int a_bits = actq[0].x, gsize = actq[0].y;
+  if (E > 1) {
+    int e = find_expert(expert_offsets, E, row);
+    a_bits = actq[e].x;
+    gsize = actq[e].y;
+    if (row >= expert_offsets[E]) return;  // rows past the last expert are not owned by anyone
+  }
+  const int64_t srow = src_row ? src_row[row] : row;
+  const __half* in = x + srow * in_pitch;
+  const int n8 = H >> 3;
+
+  if (a_bits >= 16) {
+    __half* o = out_f16 + static_cast<int64_t>(row) * H;
+    for (int i = lane; i < n8; i += 32) {
+      float v[8];
+      load8<SILU>(in, H, i, v);
+      uint4 pk;
+      __half2* ph = reinterpret_cast<__half2*>(&pk);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ph[j] = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
+      *reinterpret_cast<uint4*>(o + i * 8) = pk;
+    }
+    return;
+  }
+  const float upper = static_cast<float>((1 << (a_bits - 1)) - 1);
+  int8_t* o = out_q8 + static_cast<int64_t>(row) * H;
+  __half* so = scales + static_cast<int64_t>(row) * scale_cols;
+
+  if (gsize <= 0) {
+    float amax = 0.f;
+    for (int i = lane; i < n8; i += 32) {
+      float v[8];
+      load8<SILU>(in, H, i, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
+    }
+    amax = warp_max(amax);
+    __half sh = __float2half_rn(__fdiv_rn(amax, upper));
+    if (__half2float(sh) == 0.f) sh = __float2half(1.f);
+    const float sf = __half2float(sh);
+    if (lane == 0) so[0] = sh;
+    for (int i = lane; i < n8; i += 32) {
+      float v[8];
+      load8<SILU>(in, H, i, v);
+      uint2 pk;
+      int8_t* pb = reinterpret_cast<int8_t*>(&pk);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float q = h_round(__fdiv_rn(v[j], sf));
+        q = rintf(fminf(fmaxf(q, -upper), upper));
+        pb[j] = static_cast<int8_t>(static_cast<int>(q));
+      }
+      *reinterpret_cast<uint2*>(o + i * 8) = pk;
+    }
+  } else {
+    // gsize == 128: 16 lanes (16 x 8 elements) per group
+    const int iters = (n8 + 31) / 32;
+    for (int it = 0; it < iters; ++it) {
+      const int i = it * 32 + lane;
+      float v[8];
+      float amax = 0.f;
+      if (i < n8) {
+        load8<SILU>(in, H, i, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
+      }
+      amax = half_warp_max(amax);
+      __half sh = __float2half_rn(__fdiv_rn(amax, upper));
+      if (__half2float(sh) == 0.f) sh = __float2half(1.f);
+      const float sf = __half2float(sh);
+      if (i < n8) {
+        if ((lane & 15) == 0) so[i >> 4] = sh;
+        uint2 pk;
+        int8_t* pb = reinterpret_cast<int8_t*>(&pk);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float q = h_round(__fdiv_rn(v[j], sf));
+          q = rintf(fminf(fmaxf(q, -upper), upper));
+          pb[j] = static_cast<int8_t>(static_cast<int>(q));
+        }
+        *reinterpret_cast<uint2*>(o + i * 8) = pk;
+      }
+    }
+  }
+}
+}  // namespace
+
+cudaError_t quant_rows_launch(bool silu, const void* x, int H, int64_t in_pitch, const int32_t* src_row, int n_rows,
+                              const int32_t* expert_offsets, const int32_t* actq_dev, int E, void* out_q8, void* out_f16,
+                              void* scales, int scale_cols, cudaStream_t st) {
+  if (n_rows == 0) return cudaSuccess;
+  const int grid = (n_rows + 7) / 8;
+  if (silu)
+    quant_rows_kernel<true><<<grid, 256, 0, st>>>(static_cast<const __half*>(x), H, in_pitch, src_row, n_rows, expert_offsets,
+                                                  reinterpret_cast<const int2*>(actq_dev), E, static_cast<int8_t*>(out_q8),
+                                                  static_cast<__half*>(out_f16), static_cast<__half*>(scales), scale_cols);
+  else
+    quant_rows_kernel<false><<<grid, 256, 0, st>>>(static_cast<const __half*>(x), H, in_pitch, src_row, n_rows, expert_offsets,
+                                                   reinterpret_cast<const int2*>(actq_dev), E, static_cast<int8_t*>(out_q8),
+                                                   static_cast<__half*>(out_f16), static_cast<__half*>(scales), scale_cols);
+  return cudaGetLastError();
+}
+
+// ============================================================================ combine
+namespace {
+__global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__ down, int H, const int32_t* __restrict__ slot_of,
+                                                       const float* __restrict__ topk_w, int T, int k,
+                                                       const __half* __restrict__ shared_out, __half* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int t = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (t >= T) return;
+  const int n8 = H >> 3;
+  for (int i = lane; i < n8; i += 32) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int j = 0; j < k; ++j) {
+      const int slot = slot_of[t * k + j];
+      const float w = topk_w[t * k + j];
+      uint4 v = *reinterpret_cast<const uint4*>(down + static_cast<int64_t>(slot) * H + i * 8);
+      const __half* vh = reinterpret_cast<const __half*>(&v);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] = fmaf(w, __half2float(vh[e]), acc[e]);
+    }
+    if (shared_out != nullptr) {
+      uint4 v = *reinterpret_cast<const uint4*>(shared_out + static_cast<int64_t>(t) * H + i * 8);
+      const __half* vh = reinterpret_cast<const __half*>(&v);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] = acc[e] + __half2float(vh[e]);
+    }
+    uint4 pk;
+    __half2* ph = reinterpret_cast<__half2*>(&pk);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) ph[e] = __floats2half2_rn(acc[2 * e], acc[2 * e + 1]);
+    *reinterpret_cast<uint4*>(out + static_cast<int64_t>(t) * H + i * 8) = pk;
+  }
+}
+}  // namespace
+
+cudaError_t combine_launch(const void* down, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
+                           const void* shared_out, void* out, cudaStream_t st) {
+  if (T == 0) return cudaSuccess;
+  combine_kernel<<<(T + 7) / 8, 256, 0, st>>>(static_cast<const __half*>(down), H, slot_of, topk_w, T, k,
+                                              static_cast<const __half*>(shared_out), static_cast<__half*>(out));
+  return cudaGetLastError();
+}
+
+// ============================================================================ offline weight quantize + pack
+namespace {
+// One block per weight row.  Codes are staged in shared memory, then packed into the native layout.
+//   layout 0: int8 two's complement [N,K]                         (w8a8)
+//   layout 1: 4-bit two's complement, 32-k blocks, byte j = k j (low nibble) | k j+16 (high)   (w4a4)
+//   layout 2: unsigned 4-bit codes, nibble order 0,2,4,6,1,3,5,7 inside each 32-bit word       (w4a16)
+//   layout 3: unsigned 8-bit codes [N,K]                                                      (w8a16)
+__global__ void __launch_bounds__(256) quant_pack_weight_kernel(const __half* __restrict__ W, int N, int K, int bits, int gsize,
+                                                                 int sym, int layout, uint8_t* __restrict__ packed,
+                                                                 __half* __restrict__ scales) {
+  extern __shared__ uint8_t codes[];  // K bytes
+  const int n = blockIdx.x;
+  const int g = gsize <= 0 ? K : gsize;
+  const int G = K / g;
+  const __half* w = W + static_cast<int64_t>(n) * K;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float upper = sym ? static_cast<float>((1 << (bits - 1)) - 1) : static_cast<float>((1 << bits) - 1);
+  const float lower = sym ? -upper : 0.f;
+  for (int gi = warp; gi < G; gi += 8) {
+    float mx = -65504.f, mn = 65504.f, amx = 0.f;
+    for (int i = lane; i < g; i += 32) {
+      float v = __half2float(w[gi * g + i]);
+      mx = fmaxf(mx, v);
+      mn = fminf(mn, v);
+      amx = fmaxf(amx, fabsf(v));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      amx = fmaxf(amx, __shfl_xor_sync(0xffffffffu, amx, o));
+    }
+    float zp = sym ? 0.f : mn;
+    __half sh = sym ? __float2half_rn(__fdiv_rn(amx, upper)) : __float2half_rn(__fdiv_rn(h_round(mx - mn), upper));
+    if (__half2float(sh) == 0.f) sh = __float2half(1.f);
+    const float sf = __half2float(sh);
+    if (lane == 0) {
+      if (sym) scales[static_cast<int64_t>(gi) * N + n] = sh;
+      else {
+        scales[(static_cast<int64_t>(gi) * N + n) * 2] = sh;
+        scales[(static_cast<int64_t>(gi) * N + n) * 2 + 1] = __float2half_rn(zp);
+      }
+    }
+    const int bias = (layout >= 2 && sym) ? (1 << (bits - 1)) - 1 : 0;
+    for (int i = lane; i < g; i += 32) {
+      float v = __half2float(w[gi * g + i]);
+      float q = h_round(__fdiv_rn(h_round(v - zp), sf));
+      q = rintf(fminf(fmaxf(q, lower), upper));
+      codes[gi * g + i] = static_cast<uint8_t>(static_cast<int>(q) + bias);
+    }
+  }
+  __syncthreads();
+  if (layout == 0 || layout == 3) {
+    uint8_t* o = packed + static_cast<int64_t>(n) * K;
+    for (int i = threadIdx.x; i < K; i += 256) o[i] = codes[i];
+  } else if (layout == 1) {
+    uint8_t* o = packed + static_cast<int64_t>(n) * (K / 2);
+    for (int i = threadIdx.x; i < K / 2; i += 256) {
+      const int blk = i >> 4, j = i & 15;
+      o[i] = static_cast<uint8_t>((codes[blk * 32 + j] & 0xF) | ((codes[blk * 32 + 16 + j] & 0xF) << 4));
+    }
+  } else {
+    uint32_t* o = reinterpret_cast<uint32_t*>(packed + static_cast<int64_t>(n) * (K / 2));
+    for (int i = threadIdx.x; i < K / 8; i += 256) {
+      const uint8_t* c = codes + i * 8;
+      uint32_t wv = 0;
+      const int order[8] = {0, 2, 4, 6, 1, 3, 5, 7};
+#pragma unroll
+      for (int p = 0; p < 8; ++p) wv |= static_cast<uint32_t>(c[order[p]] & 0xF) << (4 * p);
+      o[i] = wv;
+    }
+  }
+}
+
+// Reference WxAx layout (pack_wxax, quantize.cuh:424-475): uint16 words along K, first element in the most
+// significant bits -> native layouts 0 / 1.
+__global__ void __launch_bounds__(256) repack_wxax_kernel(const uint16_t* __restrict__ ref, int N, int K, int bits,
+                                                           uint8_t* __restrict__ packed) {
+  extern __shared__ uint8_t codes[];
+  const int n = blockIdx.x;
+  const int pack = 16 / bits;
+  const uint16_t* r = ref + static_cast<int64_t>(n) * (K / pack);
+  for (int i = threadIdx.x; i < K / pack; i += 256) {
+    uint16_t wv = r[i];
+    for (int x = 0; x < pack; ++x) codes[i * pack + x] = static_cast<uint8_t>((wv >> (bits * (pack - 1 - x))) & ((1 << bits) - 1));
+  }
+  __syncthreads();
+  if (bits == 8) {
+    uint8_t* o = packed + static_cast<int64_t>(n) * K;
+    for (int i = threadIdx.x; i < K; i += 256) o[i] = codes[i];
+  } else {
+    uint8_t* o = packed + static_cast<int64_t>(n) * (K / 2);
+    for (int i = threadIdx.x; i < K / 2; i += 256) {
+      const int blk = i >> 4, j = i & 15;
+      o[i] = static_cast<uint8_t>((codes[blk * 32 + j] & 0xF) | ((codes[blk * 32 + 16 + j] & 0xF) << 4));
+    }
+  }
+}
+
+// Reference W-only layout (permute_weight + pack_weightonly, quantize.cuh:318-421) -> native layouts 2 / 3.
+// `inv` maps (row in a PACK*8-row block, k in a 16-k block) -> flat index of the value inside the
+// permuted block as it was before packing; built on the host from the reference's permutation tables.
+__global__ void __launch_bounds__(256) repack_wonly_kernel(const uint16_t* __restrict__ ref, int N, int K, int bits,
+                                                            const int32_t* __restrict__ inv, uint8_t* __restrict__ packed) {
+  extern __shared__ uint8_t codes[];
+  const int n = blockIdx.x;
+  const int pack = 16 / bits;
+  const int rows_blk = pack * 8;
+  const int nb = n / rows_blk, rin = n % rows_blk;
+  for (int kk = threadIdx.x; kk < K; kk += 256) {
+    const int kb = kk >> 4, kin = kk & 15;
+    const int src = inv[rin * 16 + kin];      // index inside the permuted [rows_blk][16] block
+    const int prow = src >> 4, pk = src & 15;  // permuted row / k
+    const int frag = prow >> 3, jj = prow & 7;
+    const uint16_t wv = ref[(static_cast<int64_t>(nb) * 8 + jj) * K + kb * 16 + pk];
+    codes[kk] = static_cast<uint8_t>((wv >> (bits * (pack - 1 - frag))) & ((1 << bits) - 1));
+  }
+  __syncthreads();
+  if (bits == 8) {
+    uint8_t* o = packed + static_cast<int64_t>(n) * K;
+    for (int i = threadIdx.x; i < K; i += 256) o[i] = codes[i];
+  } else {
+    uint32_t* o = reinterpret_cast<uint32_t*>(packed + static_cast<int64_t>(n) * (K / 2));
+    for (int i = threadIdx.x; i < K / 8; i += 256) {
+      const uint8_t* c = codes + i * 8;
+      uint32_t wv = 0;
+      const int order[8] = {0, 2, 4, 6, 1, 3, 5, 7};
+#pragma unroll
+      for (int p = 0; p < 8; ++p) wv |= static_cast<uint32_t>(c[order[p]] & 0xF) << (4 * p);
+      o[i] = wv;
+    }
+  }
+}
+}  // namespace
+
+cudaError_t quant_pack_weight_launch(const void* W, int N, int K, int bits, int gsize, int sym, int layout, void* packed,
+                                     void* scales, cudaStream_t st) {
+  quant_pack_weight_kernel<<<N, 256, K, st>>>(static_cast<const __half*>(W), N, K, bits, gsize, sym, layout,
+                                              static_cast<uint8_t*>(packed), static_cast<__half*>(scales));
+  return cudaGetLastError();
+}
+
+cudaError_t repack_wxax_launch(const void* ref, int N, int K, int bits, void* packed, cudaStream_t st) {
+  repack_wxax_kernel<<<N, 256, K, st>>>(static_cast<const uint16_t*>(ref), N, K, bits, static_cast<uint8_t*>(packed));
+  return cudaGetLastError();
+}
+
+cudaError_t repack_wonly_launch(const void* ref, int N, int K, int bits, const int32_t* inv_dev, void* packed, cudaStream_t st) {
+  repack_wonly_kernel<<<N, 256, K, st>>>(static_cast<const uint16_t*>(ref), N, K, bits, inv_dev, static_cast<uint8_t*>(packed));
+  return cudaGetLastError();
+}
+
+}  // namespace mxb

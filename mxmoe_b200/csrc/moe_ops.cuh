@@ -1,0 +1,26 @@
+// Launchers of the non-GEMM kernels (moe_ops.cu, hadamard.cu, w4a16_stream.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mxb {
+
+size_t permute_ws_bytes(int n, int E);
+cudaError_t permute_launch(const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
+                           int32_t* slot_of, int32_t* ws, cudaStream_t st);
+
+// actq_dev: device int32 pairs (a_bits, gsize) per expert
+cudaError_t quant_rows_launch(bool silu, const void* x, int H, int64_t in_pitch, const int32_t* src_row, int n_rows,
+                              const int32_t* expert_offsets, const int32_t* actq_dev, int E, void* out_q8, void* out_f16,
+                              void* scales, int scale_cols, cudaStream_t st);
+
+cudaError_t combine_launch(const void* down, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
+                           const void* shared_out, void* out, cudaStream_t st);
+
+cudaError_t quant_pack_weight_launch(const void* W, int N, int K, int bits, int gsize, int sym, int layout, void* packed,
+                                     void* scales, cudaStream_t st);
+cudaError_t repack_wxax_launch(const void* ref, int N, int K, int bits, void* packed, cudaStream_t st);
+cudaError_t repack_wonly_launch(const void* ref, int N, int K, int bits, const int32_t* inv_dev, void* packed,
+                                cudaStream_t st);
+
+}  // namespace mxb
