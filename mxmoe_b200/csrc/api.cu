@@ -1,0 +1,666 @@
+// Host side of the C-ABI (include/mxmoe_b200.h): context, plan cache, TMA tensor-map encoding and the
+// launch of the persistent grouped-GEMM kernel and the MoE helper kernels.
+//
+// Replaces the reference's generated host launcher (mxmoe/kernels/kernel_sketch.py:82-145): no per-call
+// cudaMalloc/cudaMemcpy/cudaFree of a tile prefix array (the prefix is computed on the device), no
+// exceptions, no exit(); errors come back as codes + mxb_last_error().
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/mxmoe_b200.h"
+#include "gg_kernel.cuh"
+#include "moe_ops.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CU_OK(expr)                                                                          \
+  do {                                                                                       \
+    cudaError_t e__ = (expr);                                                                \
+    if (e__ != cudaSuccess) return fail(MXB_ECUDA, "%s: %s", #expr, cudaGetErrorString(e__)); \
+  } while (0)
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+uint64_t fnv1a(const void* p, size_t n, uint64_t h = 1469598103934665603ull) {
+  const uint8_t* b = static_cast<const uint8_t*>(p);
+  for (size_t i = 0; i < n; ++i) {
+    h ^= b[i];
+    h *= 1099511628211ull;
+  }
+  return h;
+}
+
+struct Plan {
+  uint64_t key = 0;
+  int P = 0;
+  mxb::DevProblem* dev = nullptr;  // device array, capacity GG_MAXP per chunk list
+  size_t cap = 0;
+  uint64_t last_use = 0;
+};
+
+struct DevTable {  // small constant tables mirrored on the device, keyed by content
+  uint64_t key = 0;
+  void* dev = nullptr;
+  size_t bytes = 0;
+  uint64_t last_use = 0;
+};
+
+}  // namespace
+
+struct mxb_context {
+  int device = 0;
+  int sm_count = 0;
+  EncodeTiledFn encode = nullptr;
+  std::vector<Plan> plans;
+  std::vector<DevTable> tables;
+  uint64_t tick = 0;
+  int32_t* ws = nullptr;  // permute workspace
+  size_t ws_bytes = 0;
+  int32_t* inv_tab[3] = {nullptr, nullptr, nullptr};  // repack tables for 8/4/2-bit W-only reference layout
+  std::vector<std::pair<int, void*>> hads;            // device fp16 copies of the K x K Hadamard factors
+};
+
+namespace {
+
+constexpr int kMaxPlans = 64;
+constexpr int kMaxTables = 64;
+
+// Encode a 2-D row-major tensor [rows, inner_elems] with a [box_rows, box_inner] box.
+int encode_2d(mxb_context* c, CUtensorMap* tm, CUtensorMapDataType dt, int elsize, const void* base, uint64_t inner_elems,
+              uint64_t rows, uint64_t pitch_bytes, uint32_t box_inner, uint32_t box_rows, bool swizzle128) {
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return fail(MXB_EINVAL, "operand pointer %p is not 16-byte aligned", base);
+  if (pitch_bytes % 16 != 0) return fail(MXB_EINVAL, "operand row pitch %llu B is not a multiple of 16", (unsigned long long)pitch_bytes);
+  if (rows == 0) rows = 1;  // an empty problem never issues a load; keep the descriptor encodable
+  cuuint64_t gdim[2] = {inner_elems, rows};
+  cuuint64_t gstr[1] = {pitch_bytes};
+  cuuint32_t box[2] = {box_inner, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  (void)elsize;
+  CUresult r = c->encode(tm, dt, 2, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(MXB_ECUDA, "cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] box [%u x %u]", (int)r,
+                                     (unsigned long long)rows, (unsigned long long)inner_elems, box_rows, box_inner);
+  return MXB_OK;
+}
+
+struct KindInfo {
+  int mma_kind, conv, epi, acc_shift;
+  int a_elsize;        // bytes per A element in HBM (2 fp16, 1 int8)
+  int k_per_block;     // K elements per 128-byte MMA slab
+  int b_bytes_per_kb;  // bytes of B per row per k-block as stored in HBM
+};
+
+// (w_bits, a_bits, gsize, sym) -> pipeline, the run-time equivalent of CTA_KERNEL_MAP / BRANCH_CONDITION_MAP
+// (mxmoe/kernels/compose_kernel.py:22-57).  Unsupported combinations are an error like compose_kernel.py:433.
+int classify(const MxbProblem& p, KindInfo* k) {
+  const int w = p.w_bits, a = p.a_bits, g = p.gsize;
+  if (g != -1 && g != 128) return fail(MXB_EINVAL, "quant type not supported: gsize %d (only -1 or 128)", g);
+  if (w == 16 && a == 16) {
+    *k = {mxb::MMA_F16, mxb::CONV_NONE, mxb::EPI_F32, 0, 2, 64, 128};
+    return MXB_OK;
+  }
+  if (a == 16 && (w == 4 || w == 8)) {
+    *k = {mxb::MMA_F16, w == 4 ? mxb::CONV_W4_F16 : mxb::CONV_W8_F16, mxb::EPI_F32, 0, 2, 64, w == 4 ? 32 : 64};
+    return MXB_OK;
+  }
+  if (a == 8 && w == 8 && p.sym) {
+    *k = {mxb::MMA_I8, mxb::CONV_NONE, g == -1 ? mxb::EPI_INT_ROWCOL : mxb::EPI_INT_GROUP, 0, 1, 128, 128};
+    return MXB_OK;
+  }
+  if (a == 4 && w == 4 && p.sym) {
+    *k = {mxb::MMA_I8, mxb::CONV_W4_I8, g == -1 ? mxb::EPI_INT_ROWCOL : mxb::EPI_INT_GROUP, 4, 1, 128, 64};
+    return MXB_OK;
+  }
+  return fail(MXB_EINVAL, "quant type not supported: w%da%d_g%d_%s", w, a, g, p.sym ? "sym" : "asym");
+}
+
+int pick_tile_n(const MxbProblem& p, const KindInfo& k) {
+  int cap = 256;
+  if (k.conv != mxb::CONV_NONE) cap = 128;
+  if (k.epi == mxb::EPI_INT_GROUP) cap = 64;
+  int bn = p.tile_n > 0 ? p.tile_n : cap;
+  if (bn > cap) bn = cap;
+  int n32 = (p.N + 31) / 32 * 32;
+  if (bn > n32) bn = n32;
+  if (bn >= 256) bn = 256;
+  else if (bn >= 128) bn = 128;
+  else if (bn >= 64) bn = 64;
+  else bn = 32;
+  return bn;
+}
+
+int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, mxb::DevProblem* d) {
+  memset(d, 0, sizeof *d);
+  KindInfo k = {};
+  int rc = classify(p, &k);
+  if (rc) return rc;
+  if (p.M < 0 || p.N <= 0 || p.K <= 0) return fail(MXB_EINVAL, "bad problem size %d x %d x %d", p.M, p.N, p.K);
+  if (p.N % 8 != 0) return fail(MXB_EINVAL, "N=%d must be a multiple of 8", p.N);
+  if (p.K % 32 != 0) return fail(MXB_EINVAL, "K=%d must be a multiple of 32", p.K);
+  if (p.gsize == 128 && p.K % 128 != 0) return fail(MXB_EINVAL, "K=%d must be a multiple of the group size 128", p.K);
+  if (!p.A || !p.B || !p.C) return fail(MXB_EINVAL, "null operand pointer");
+  if (k.epi != mxb::EPI_F32 && (!p.scale_a || !p.scale_b)) return fail(MXB_EINVAL, "quantized problem without scales");
+  if (k.conv >= mxb::CONV_W4_F16 && !p.scale_b) return fail(MXB_EINVAL, "weight-only problem without scale_b");
+  const int bn = pick_tile_n(p, k);
+  const int64_t lda = p.lda > 0 ? p.lda : p.K;
+  d->scale_a = static_cast<const __half*>(p.scale_a);
+  d->scale_b = static_cast<const __half*>(p.scale_b);
+  d->C = static_cast<__half*>(p.C);
+  d->acc_out = acc_out;
+  d->m_range = p.m_range;
+  d->ldc = p.ldc > 0 ? p.ldc : p.N;
+  d->M = p.M;
+  d->N = p.N;
+  d->K = p.K;
+  d->mma_kind = k.mma_kind;
+  d->conv = k.conv;
+  d->epi = k.epi;
+  d->acc_shift = k.acc_shift;
+  d->bn = bn;
+  d->n_tiles = (p.N + bn - 1) / bn;
+  d->kblocks = (p.K + k.k_per_block - 1) / k.k_per_block;
+  d->a_kstep = k.k_per_block;  // A map dtype has one element per K element
+  d->b_kstep = k.conv == mxb::CONV_NONE ? k.k_per_block : k.b_bytes_per_kb;
+  d->tx_bytes = mxb::GG_A_BYTES + bn * k.b_bytes_per_kb;
+  d->gsize = p.gsize;
+  d->sym = p.sym;
+  d->scale_a_ld = (k.epi == mxb::EPI_INT_GROUP) ? p.K / 128 : 1;
+  if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k
+  else if (k.conv >= mxb::CONV_W4_F16) d->kb_per_group = p.gsize == 128 ? 2 : d->kblocks;  // fp16 slabs hold 64 k
+  else d->kb_per_group = d->kblocks;
+  if (d->kb_per_group < 1) d->kb_per_group = 1;
+  const uint32_t cfmt = k.mma_kind == mxb::MMA_I8 ? 2u : 1u;
+  const uint32_t abfmt = k.mma_kind == mxb::MMA_I8 ? 1u : 0u;
+  d->idesc = (cfmt << 4) | (abfmt << 7) | (abfmt << 10) | ((uint32_t(bn) >> 3) << 17) | ((128u >> 4) << 24);
+
+  // A: [rows, K] of fp16 or int8, 128-byte swizzled box of 128 rows
+  const CUtensorMapDataType adt = k.a_elsize == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  rc = encode_2d(c, &d->tmA, adt, k.a_elsize, p.A, p.K, p.M, lda * k.a_elsize, k.k_per_block, 128, true);
+  if (rc) return rc;
+  if (k.conv == mxb::CONV_NONE) {
+    rc = encode_2d(c, &d->tmB, adt, k.a_elsize, p.B, p.K, p.N, uint64_t(p.K) * k.a_elsize, k.k_per_block, bn, true);
+  } else {
+    const uint64_t row_bytes = uint64_t(p.K) * p.w_bits / 8;
+    rc = encode_2d(c, &d->tmB, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p.B, row_bytes, p.N, row_bytes, k.b_bytes_per_kb, bn, false);
+  }
+  return rc;
+}
+
+}  // namespace
+
+// ============================================================================ exported C-ABI
+namespace {
+
+int device_table(mxb_context* c, const void* host, size_t bytes, cudaStream_t st, void** out) {
+  const uint64_t key = fnv1a(host, bytes) ^ (uint64_t(bytes) << 48);
+  ++c->tick;
+  for (auto& t : c->tables)
+    if (t.key == key && t.bytes == bytes) {
+      t.last_use = c->tick;
+      *out = t.dev;
+      return MXB_OK;
+    }
+  DevTable* slot = nullptr;
+  if ((int)c->tables.size() < kMaxTables) {
+    c->tables.emplace_back();
+    slot = &c->tables.back();
+  } else {
+    slot = &c->tables[0];
+    for (auto& t : c->tables)
+      if (t.last_use < slot->last_use) slot = &t;
+    // the evicted table may still be read by work queued earlier on another stream
+    CU_OK(cudaDeviceSynchronize());
+    cudaFree(slot->dev);
+    slot->dev = nullptr;
+  }
+  CU_OK(cudaMalloc(&slot->dev, bytes < 256 ? 256 : bytes));
+  CU_OK(cudaMemcpyAsync(slot->dev, host, bytes, cudaMemcpyHostToDevice, st));
+  slot->key = key;
+  slot->bytes = bytes;
+  slot->last_use = c->tick;
+  *out = slot->dev;
+  return MXB_OK;
+}
+
+int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* acc_out, cudaStream_t st, Plan** out) {
+  uint64_t key = fnv1a(problems, sizeof(MxbProblem) * size_t(P));
+  if (acc_out) key = fnv1a(acc_out, sizeof(int32_t*) * size_t(P), key ^ 0x9e3779b97f4a7c15ull);
+  ++c->tick;
+  for (auto& pl : c->plans)
+    if (pl.key == key && pl.P == P) {
+      pl.last_use = c->tick;
+      *out = &pl;
+      return MXB_OK;
+    }
+  std::vector<mxb::DevProblem> host(static_cast<size_t>(P));
+  for (int i = 0; i < P; ++i) {
+    int rc = build_dev_problem(c, problems[i], acc_out ? acc_out[i] : nullptr, &host[i]);
+    if (rc) {
+      std::string m = g_err;
+      return fail(rc, "problem %d: %s", i, m.c_str());
+    }
+  }
+  Plan* slot = nullptr;
+  if ((int)c->plans.size() < kMaxPlans) {
+    c->plans.emplace_back();
+    slot = &c->plans.back();
+  } else {
+    slot = &c->plans[0];
+    for (auto& pl : c->plans)
+      if (pl.last_use < slot->last_use) slot = &pl;
+    CU_OK(cudaDeviceSynchronize());  // the evicted plan may still be in use by queued launches
+  }
+  if (slot->cap < size_t(P)) {
+    if (slot->dev) cudaFree(slot->dev);
+    slot->dev = nullptr;
+    slot->cap = 0;
+    CU_OK(cudaMalloc(reinterpret_cast<void**>(&slot->dev), sizeof(mxb::DevProblem) * size_t(P)));
+    slot->cap = size_t(P);
+  }
+  // pageable source: the runtime stages the bytes before returning, so `host` may die right after
+  CU_OK(cudaMemcpyAsync(slot->dev, host.data(), sizeof(mxb::DevProblem) * size_t(P), cudaMemcpyHostToDevice, st));
+  slot->key = key;
+  slot->P = P;
+  slot->last_use = c->tick;
+  *out = slot;
+  return MXB_OK;
+}
+
+int group_gemm_impl(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* acc_out, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (P < 0 || (P > 0 && !problems)) return fail(MXB_EINVAL, "bad problem list");
+  if (P == 0) return MXB_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU_OK(cudaSetDevice(c->device));
+  Plan* pl = nullptr;
+  int rc = get_plan(c, problems, P, acc_out, st, &pl);
+  if (rc) return rc;
+  for (int off = 0; off < P; off += mxb::GG_MAXP) {
+    const int n = P - off < mxb::GG_MAXP ? P - off : mxb::GG_MAXP;
+    mxb::gg_launch(pl->dev + off, n, c->sm_count, st);
+  }
+  CU_OK(cudaGetLastError());
+  return MXB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* mxb_last_error(void) { return g_err.c_str(); }
+const char* mxb_version(void) { return "mxmoe_b200 0.1 (sm_100a)"; }
+
+int mxb_create(int device, mxb_handle_t* out) {
+  if (!out) return fail(MXB_EINVAL, "null out");
+  *out = nullptr;
+  CU_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU_OK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(MXB_EUNSUPPORTED, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+  mxb_context* c = new (std::nothrow) mxb_context();
+  if (!c) return fail(MXB_ENOMEM, "out of host memory");
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || fn == nullptr || qres != cudaDriverEntryPointSuccess) {
+    delete c;
+    return fail(MXB_ECUDA, "cuTensorMapEncodeTiled entry point not available");
+  }
+  c->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  e = static_cast<cudaError_t>(mxb::gg_configure());
+  if (e != cudaSuccess) {
+    delete c;
+    return fail(MXB_ECUDA, "cudaFuncSetAttribute(max dynamic smem %d): %s", mxb::GG_SMEM_BYTES, cudaGetErrorString(e));
+  }
+  c->ws_bytes = 8u << 20;
+  e = cudaMalloc(reinterpret_cast<void**>(&c->ws), c->ws_bytes);
+  if (e != cudaSuccess) {
+    delete c;
+    return fail(MXB_ENOMEM, "workspace allocation failed: %s", cudaGetErrorString(e));
+  }
+  cudaMemset(c->ws, 0, c->ws_bytes);
+  c->plans.reserve(kMaxPlans);
+  c->tables.reserve(kMaxTables);
+  *out = c;
+  return MXB_OK;
+}
+
+int mxb_destroy(mxb_handle_t c) {
+  if (!c) return MXB_OK;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (auto& pl : c->plans)
+    if (pl.dev) cudaFree(pl.dev);
+  for (auto& t : c->tables)
+    if (t.dev) cudaFree(t.dev);
+  for (auto* p : c->inv_tab)
+    if (p) cudaFree(p);
+  for (auto& h : c->hads) cudaFree(h.second);
+  if (c->ws) cudaFree(c->ws);
+  delete c;
+  return MXB_OK;
+}
+
+int mxb_sm_count(mxb_handle_t c) { return c ? c->sm_count : 0; }
+
+int mxb_group_gemm(mxb_handle_t c, const MxbProblem* problems, int problem_count, void* stream) {
+  return group_gemm_impl(c, problems, problem_count, nullptr, stream);
+}
+
+int mxb_group_gemm_debug_acc(mxb_handle_t c, const MxbProblem* problems, int problem_count, int32_t* const* acc_out,
+                             void* stream) {
+  return group_gemm_impl(c, problems, problem_count, acc_out, stream);
+}
+
+int mxb_group_gemm_reflayout(mxb_handle_t c, void** ptr_As, void** ptr_Bs, void** ptr_scale_a, void** ptr_scale_b,
+                             void** ptr_Cs, void** ptr_Ds, int64_t* ldas, int64_t* ldbs, int64_t* ldcs, int64_t* ldds,
+                             const void* dev_problem_sizes, const void* host_problem_sizes, const void* dev_qparams,
+                             const void* host_qparams, int P, void* stream) {
+  (void)ptr_Ds; (void)ldas; (void)ldbs; (void)ldcs; (void)ldds; (void)dev_problem_sizes; (void)dev_qparams;  // unused by the reference too
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (P <= 0) return P == 0 ? MXB_OK : fail(MXB_EINVAL, "negative problem count");
+  if (!host_problem_sizes || !host_qparams) return fail(MXB_EINVAL, "host copies of sizes/qparams are required");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  std::vector<void*> hA(P), hB(P), hSa(P), hSb(P), hC(P);
+  // the pointer tables live on the device in the reference's contract: fetch them (synchronous, like the
+  // reference launcher's own cudaMemcpy)
+  CU_OK(cudaMemcpyAsync(hA.data(), ptr_As, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
+  CU_OK(cudaMemcpyAsync(hB.data(), ptr_Bs, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
+  CU_OK(cudaMemcpyAsync(hC.data(), ptr_Cs, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
+  if (ptr_scale_a) CU_OK(cudaMemcpyAsync(hSa.data(), ptr_scale_a, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
+  if (ptr_scale_b) CU_OK(cudaMemcpyAsync(hSb.data(), ptr_scale_b, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
+  CU_OK(cudaStreamSynchronize(st));
+  struct Dim3 { uint32_t x, y, z; };
+  struct QP { int32_t a_bits, w_bits, gsize; uint8_t sym; uint8_t pad[3]; };
+  const Dim3* sz = static_cast<const Dim3*>(host_problem_sizes);
+  const QP* qp = static_cast<const QP*>(host_qparams);
+  std::vector<MxbProblem> pr;
+  pr.reserve(P);
+  for (int i = 0; i < P; ++i) {
+    if (sz[i].x == 0) continue;  // the reference's callers skip empty problems (ref_bind.cu:360)
+    MxbProblem p;
+    memset(&p, 0, sizeof p);
+    p.A = hA[i]; p.B = hB[i]; p.C = hC[i];
+    p.scale_a = ptr_scale_a ? hSa[i] : nullptr;
+    p.scale_b = ptr_scale_b ? hSb[i] : nullptr;
+    p.M = (int)sz[i].x; p.N = (int)sz[i].y; p.K = (int)sz[i].z;
+    p.a_bits = qp[i].a_bits; p.w_bits = qp[i].w_bits; p.gsize = qp[i].gsize; p.sym = qp[i].sym ? 1 : 0;
+    if (p.a_bits == 16 && p.w_bits == 16) { p.gsize = -1; p.sym = 1; }
+    pr.push_back(p);
+  }
+  return group_gemm_impl(c, pr.data(), (int)pr.size(), nullptr, stream);
+}
+
+}  // extern "C"
+
+// ============================================================================ MoE helper ops + offline weight path
+namespace {
+
+int actq_table(mxb_context* c, const MxbActQ* actq, int E, cudaStream_t st, const int32_t** dev, int* any_g128, int* any_q,
+               int* any_f16) {
+  *any_g128 = *any_q = *any_f16 = 0;
+  for (int e = 0; e < E; ++e) {
+    const int a = actq[e].a_bits, g = actq[e].gsize;
+    if (!(a == 16 || a == 8 || a == 4)) return fail(MXB_EINVAL, "expert %d: a_bits %d not supported (16, 8, 4)", e, a);
+    if (a != 16 && g != -1 && g != 128) return fail(MXB_EINVAL, "expert %d: activation gsize %d not supported (-1, 128)", e, g);
+    if (a == 16) *any_f16 = 1; else *any_q = 1;
+    if (a != 16 && g == 128) *any_g128 = 1;
+  }
+  void* d = nullptr;
+  int rc = device_table(c, actq, sizeof(MxbActQ) * size_t(E), st, &d);
+  *dev = static_cast<const int32_t*>(d);
+  return rc;
+}
+
+#include "hadk_data.inc"
+
+// fp16 copy of the reference's K x K factor, zero padded to a multiple of 16, cached per K on the device
+int hadamard_matrix(mxb_context* c, int K, const void** dev, int* Kp_out) {
+  const int Kp = (K + 15) / 16 * 16;
+  *Kp_out = Kp;
+  for (auto& h : c->hads)
+    if (h.first == K) {
+      *dev = h.second;
+      return MXB_OK;
+    }
+  const unsigned char* bits = nullptr;
+  for (int i = 0; i < kHadTableSize; ++i)
+    if (kHadTable[i].k == K) bits = kHadTable[i].bits;
+  if (!bits) return fail(MXB_EINVAL, "no Hadamard matrix of order %d", K);
+  std::vector<__half> h(size_t(Kp) * Kp, __float2half(0.f));
+  for (int i = 0; i < K; ++i)
+    for (int j = 0; j < K; ++j) {
+      const int b = i * K + j;
+      const int bit = (bits[b >> 3] >> (7 - (b & 7))) & 1;
+      h[size_t(i) * Kp + j] = __float2half(bit ? 1.f : -1.f);
+    }
+  void* d = nullptr;
+  CU_OK(cudaMalloc(&d, h.size() * sizeof(__half)));
+  CU_OK(cudaMemcpy(d, h.data(), h.size() * sizeof(__half), cudaMemcpyHostToDevice));
+  c->hads.emplace_back(K, d);
+  *dev = d;
+  return MXB_OK;
+}
+
+int quant_common(mxb_context* c, bool silu, const void* x, int H, const int32_t* src_row, int n_rows,
+                 const int32_t* expert_offsets, const MxbActQ* actq, int E, int hadamard, void* out_q8, void* out_f16,
+                 void* scales, int scale_cols, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (!x || !actq || E < 1 || n_rows < 0) return fail(MXB_EINVAL, "bad argument");
+  if (H % 8 != 0) return fail(MXB_EINVAL, "row length %d must be a multiple of 8", H);
+  if (E > 1 && !expert_offsets) return fail(MXB_EINVAL, "expert_offsets required when E > 1");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU_OK(cudaSetDevice(c->device));
+  const int32_t* tab = nullptr;
+  int g128, anyq, anyf;
+  int rc = actq_table(c, actq, E, st, &tab, &g128, &anyq, &anyf);
+  if (rc) return rc;
+  if (anyq && (!out_q8 || !scales)) return fail(MXB_EINVAL, "quantized experts need out_q8 and scales");
+  if (anyf && !out_f16) return fail(MXB_EINVAL, "fp16 experts need out_f16");
+  if (g128 && (H % 128 != 0 || scale_cols < H / 128)) return fail(MXB_EINVAL, "gsize 128 needs H %% 128 == 0 and scale_cols >= H/128");
+  if (scale_cols < 1) scale_cols = 1;
+  if (hadamard) {
+    const int K = mxb::hadamard_factor(H);
+    if (K == 0) return fail(MXB_EINVAL, "no Hadamard factorisation for row length %d (get_hadK would assert)", H);
+    if (K > 1 && H / K < 8) return fail(MXB_EINVAL, "Hadamard row length %d = %d x %d: power-of-two part below 8 not supported", H, K, H / K);
+    const void* hmat = nullptr;
+    int Kp = 16;
+    if (K > 1) {
+      rc = hadamard_matrix(c, K, &hmat, &Kp);
+      if (rc) return rc;
+    }
+    cudaError_t e = mxb::hadamard_quant_launch(silu, x, H, src_row, n_rows, expert_offsets, tab, E, out_q8, out_f16, scales,
+                                               scale_cols, hmat, K, Kp, c->sm_count, st);
+    if (e != cudaSuccess) return fail(MXB_ECUDA, "hadamard_quant_launch: %s", cudaGetErrorString(e));
+    return MXB_OK;
+  }
+  const int64_t pitch = silu ? 2 * int64_t(H) : int64_t(H);
+  CU_OK(mxb::quant_rows_launch(silu, x, H, pitch, src_row, n_rows, expert_offsets, tab, E, out_q8, out_f16, scales, scale_cols, st));
+  return MXB_OK;
+}
+
+// (row in a PACK*8-row block, k in a 16-k block) -> position of that value inside the reference's permuted
+// block; restates the index arithmetic of permute_weight (quantize.cuh:318-381, PermuteMode::Row).
+void build_inv_table(int bits, std::vector<int32_t>* inv) {
+  const int pack = 16 / bits;
+  const int n = 4 * pack, plen = n / 2;
+  static const int proj8[4] = {1, 0, 3, 2};
+  static const int des8[8] = {0, 2, 4, 6, 1, 3, 5, 7};
+  static const int proj4[8] = {3, 7, 2, 6, 1, 5, 0, 4};
+  static const int des4[16] = {0, 4, 8, 12, 1, 5, 9, 13, 2, 6, 10, 14, 3, 7, 11, 15};
+  static const int proj2[16] = {7, 15, 6, 14, 5, 13, 4, 12, 3, 11, 2, 10, 1, 9, 0, 8};
+  static const int des2[32] = {0, 8, 16, 24, 1, 9, 17, 25, 2, 10, 18, 26, 3, 11, 19, 27,
+                               4, 12, 20, 28, 5, 13, 21, 29, 6, 14, 22, 30, 7, 15, 23, 31};
+  const int* proj = bits == 8 ? proj8 : bits == 4 ? proj4 : proj2;
+  const int* des = bits == 8 ? des8 : bits == 4 ? des4 : des2;
+  std::vector<int> perm(n);
+  for (int i = 0; i < n; i += plen)
+    for (int j = 0; j < plen; ++j) perm[proj[j] + i] = des[i + j];
+  inv->assign(size_t(pack) * 8 * 16, 0);
+  auto coord = [&](int x, int tj, int ti, int* row, int* k) {
+    const int frag = x % pack, rest = x / pack;  // x = (ii*2 + trav_ii)*pack + frag
+    const int tii = rest % 2, ii = rest / 2;
+    *row = frag * 8 + tj;
+    *k = ii * 8 + ti * 2 + tii;
+  };
+  for (int tj = 0; tj < 8; ++tj)
+    for (int ti = 0; ti < 4; ++ti)
+      for (int x = 0; x < n; ++x) {
+        int prow, pk, r, kin;
+        coord(x, tj, ti, &prow, &pk);        // where the value lands
+        coord(perm[x], tj, ti, &r, &kin);    // where it came from
+        (*inv)[size_t(r) * 16 + kin] = prow * 16 + pk;
+      }
+}
+
+int native_layout(int w_bits, int a_bits) {
+  if (a_bits < 16) return w_bits == 8 ? 0 : (w_bits == 4 ? 1 : -1);
+  return w_bits == 4 ? 2 : (w_bits == 8 ? 3 : -1);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mxb_permute(mxb_handle_t c, const int32_t* topk_ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
+                int32_t* slot_of, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (T < 0 || k < 1 || E < 1 || E > 1024) return fail(MXB_EINVAL, "bad permute shape T=%d k=%d E=%d (E <= 1024)", T, k, E);
+  if (!expert_offsets || (T > 0 && (!topk_ids || !src_row || !slot_of))) return fail(MXB_EINVAL, "null pointer");
+  if (mxb::permute_ws_bytes(T * k, E) > c->ws_bytes) return fail(MXB_ENOMEM, "permute workspace too small for T*k=%d, E=%d", T * k, E);
+  CU_OK(cudaSetDevice(c->device));
+  CU_OK(mxb::permute_launch(topk_ids, T, k, E, expert_offsets, src_row, slot_of, c->ws, static_cast<cudaStream_t>(stream)));
+  return MXB_OK;
+}
+
+int mxb_quant_act(mxb_handle_t c, const void* x, int H, const int32_t* src_row, int n_rows, const int32_t* expert_offsets,
+                  const MxbActQ* actq, int E, int hadamard, void* out_q8, void* out_f16, void* scales, int scale_cols,
+                  void* stream) {
+  return quant_common(c, false, x, H, src_row, n_rows, expert_offsets, actq, E, hadamard, out_q8, out_f16, scales, scale_cols, stream);
+}
+
+int mxb_silu_mul_quant(mxb_handle_t c, const void* gate_up, int I, int n_rows, const int32_t* expert_offsets,
+                       const MxbActQ* actq, int E, int hadamard, void* out_q8, void* out_f16, void* scales, int scale_cols,
+                       void* stream) {
+  return quant_common(c, true, gate_up, I, nullptr, n_rows, expert_offsets, actq, E, hadamard, out_q8, out_f16, scales, scale_cols, stream);
+}
+
+int mxb_combine(mxb_handle_t c, const void* down_out, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
+                const void* shared_out, void* out, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (T < 0 || k < 1 || H % 8 != 0) return fail(MXB_EINVAL, "bad combine shape T=%d k=%d H=%d", T, k, H);
+  if (T > 0 && (!down_out || !slot_of || !topk_w || !out)) return fail(MXB_EINVAL, "null pointer");
+  CU_OK(cudaSetDevice(c->device));
+  CU_OK(mxb::combine_launch(down_out, H, slot_of, topk_w, T, k, shared_out, out, static_cast<cudaStream_t>(stream)));
+  return MXB_OK;
+}
+
+int64_t mxb_packed_bytes(int N, int K, int w_bits) { return int64_t(N) * K * w_bits / 8; }
+
+int64_t mxb_scale_elems(int N, int K, int w_bits, int a_bits, int gsize, int sym) {
+  (void)w_bits; (void)a_bits;
+  const int64_t G = gsize <= 0 ? 1 : K / gsize;
+  return G * N * (sym ? 1 : 2);
+}
+
+int mxb_quant_pack_weight(mxb_handle_t c, const void* W, int N, int K, int w_bits, int a_bits, int gsize, int sym, void* packed,
+                          void* scales, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  const int layout = native_layout(w_bits, a_bits);
+  if (layout < 0) return fail(MXB_EINVAL, "quant type not supported: w%da%d", w_bits, a_bits);
+  if (a_bits < 16 && !sym) return fail(MXB_EINVAL, "quant type not supported: asymmetric WxAx");
+  if (K % 32 != 0 || (gsize > 0 && K % gsize != 0) || K > 96 * 1024) return fail(MXB_EINVAL, "bad K=%d for gsize %d", K, gsize);
+  if (!W || !packed || !scales) return fail(MXB_EINVAL, "null pointer");
+  CU_OK(cudaSetDevice(c->device));
+  CU_OK(mxb::quant_pack_weight_launch(W, N, K, w_bits, gsize, sym, layout, packed, scales, static_cast<cudaStream_t>(stream)));
+  return MXB_OK;
+}
+
+int mxb_repack_from_ref(mxb_handle_t c, const void* ref_packed, int N, int K, int w_bits, int a_bits, int sym, void* packed,
+                        void* stream) {
+  (void)sym;  // the bias of symmetric W-only codes is the same in both layouts
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  const int layout = native_layout(w_bits, a_bits);
+  if (layout < 0) return fail(MXB_EINVAL, "quant type not supported: w%da%d", w_bits, a_bits);
+  if (!ref_packed || !packed) return fail(MXB_EINVAL, "null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU_OK(cudaSetDevice(c->device));
+  if (a_bits < 16) {
+    if (K % 32 != 0) return fail(MXB_EINVAL, "K=%d must be a multiple of 32", K);
+    CU_OK(mxb::repack_wxax_launch(ref_packed, N, K, w_bits, packed, st));
+    return MXB_OK;
+  }
+  const int pack = 16 / w_bits;
+  if (N % (pack * 8) != 0 || K % 16 != 0) return fail(MXB_EINVAL, "reference W-only layout needs N %% %d == 0 and K %% 16 == 0", pack * 8);
+  const int slot = w_bits == 8 ? 0 : 1;
+  if (!c->inv_tab[slot]) {
+    std::vector<int32_t> inv;
+    build_inv_table(w_bits, &inv);
+    CU_OK(cudaMalloc(reinterpret_cast<void**>(&c->inv_tab[slot]), inv.size() * 4));
+    CU_OK(cudaMemcpy(c->inv_tab[slot], inv.data(), inv.size() * 4, cudaMemcpyHostToDevice));
+  }
+  CU_OK(mxb::repack_wonly_launch(ref_packed, N, K, w_bits, c->inv_tab[slot], packed, st));
+  return MXB_OK;
+}
+
+}  // extern "C"
+
+// ============================================================================ Blackwell tile selector / cost model
+// Replaces the hand-curated sm80/sm89 tile lists (mxmoe/kernels/tile_config.py:330-610) and the hard-coded
+// "best tiles" of bits_solver.py:425-515.  On sm_100 the MMA atom is fixed by the hardware (UMMA 128 x N x 32 B),
+// so the choice reduces to tile N, the path (tensor-core GroupGEMM vs HBM-streaming weight-only) and a roofline
+// estimate that the bit-width solver can use as T[e][n][s] (bits_solver.py:518-542).
+extern "C" int mxb_select_tiles(mxb_handle_t c, const MxbProblem* problems, int P, MxbTileChoice* out) {
+  if (P < 0 || (P > 0 && (!problems || !out))) return fail(MXB_EINVAL, "bad argument");
+  const double sms = c ? c->sm_count : 148;
+  const double clk = 1.5e9;                       // sustained SM clock under load (MEASURED_PEAKS.json: 1.3-1.5 GHz)
+  const double hbm = 6.5e12;                      // measured copy bandwidth, B/s
+  for (int i = 0; i < P; ++i) {
+    const MxbProblem& p = problems[i];
+    KindInfo k = {};
+    int rc = classify(p, &k);
+    if (rc) return rc;
+    MxbTileChoice t;
+    t.tile_m = 128;
+    t.tile_n = pick_tile_n(p, k);
+    t.tile_k = k.k_per_block;
+    t.stages = mxb::GG_STAGES;
+    t.path = (p.a_bits == 16 && p.w_bits == 4 && p.M <= 16) ? 1 : 0;
+    // tensor time: tiles x k-slabs x 4 MMAs x (128*N/256) cycles each (B300_MICROARCH "tcgen05 floor"), spread over the SMs
+    const double tiles = double((p.M + 127) / 128) * double((p.N + t.tile_n - 1) / t.tile_n);
+    const double kb = double((p.K + k.k_per_block - 1) / k.k_per_block);
+    double cyc = tiles * kb * 4.0 * (128.0 * t.tile_n / 256.0);
+    if (k.epi == mxb::EPI_INT_GROUP) cyc *= 2.0;  // epilogue-paced: one TMEM drain per 128-K group
+    const double t_tensor = cyc / (sms * clk);
+    const double bytes = double(p.N) * p.K * p.w_bits / 8.0 + double(p.M) * p.K * (p.a_bits >= 8 ? (p.a_bits == 16 ? 2 : 1) : 1) +
+                         double(p.M) * p.N * 2.0;
+    const double t_mem = bytes / hbm;
+    t.est_us = float(1e6 * (t_tensor > t_mem ? t_tensor : t_mem));
+    out[i] = t;
+  }
+  return MXB_OK;
+}

@@ -14,6 +14,7 @@
 #include <stdint.h>
 
 #include "moe_ops.cuh"
+#include "quant_common.cuh"
 
 namespace mxb {
 
@@ -143,52 +144,6 @@ cudaError_t permute_launch(const int32_t* ids, int T, int k, int E, int32_t* exp
 
 // ============================================================================ per-token quantization
 namespace {
-
-__device__ __forceinline__ float warp_max(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
-}
-__device__ __forceinline__ float half_warp_max(float v) {  // reduce inside each group of 16 lanes
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
-}
-
-// torch-CPU fp16 semantics: every op computes in fp32 and rounds to fp16 (quant.py:66-82 on a half tensor)
-__device__ __forceinline__ float h_round(float x) { return __half2float(__float2half_rn(x)); }
-__device__ __forceinline__ float silu_mul_h(__half g, __half u) {
-  float gf = __half2float(g);
-  float s = h_round(__fdiv_rn(gf, 1.f + expf(-gf)));
-  return h_round(s * __half2float(u));
-}
-
-template <bool SILU>
-__device__ __forceinline__ void load8(const __half* __restrict__ row, int H, int idx8, float (&x)[8]) {
-  if (SILU) {
-    uint4 g = *reinterpret_cast<const uint4*>(row + idx8 * 8);
-    uint4 u = *reinterpret_cast<const uint4*>(row + H + idx8 * 8);
-    const __half* gh = reinterpret_cast<const __half*>(&g);
-    const __half* uh = reinterpret_cast<const __half*>(&u);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) x[j] = silu_mul_h(gh[j], uh[j]);
-  } else {
-    uint4 v = *reinterpret_cast<const uint4*>(row + idx8 * 8);
-    const __half* vh = reinterpret_cast<const __half*>(&v);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) x[j] = __half2float(vh[j]);
-  }
-}
-
-__device__ __forceinline__ int find_expert(const int32_t* __restrict__ offs, int E, int row) {
-  int lo = 0, hi = E;  // largest e with offs[e] <= row
-  while (hi - lo > 1) {
-    int mid = (lo + hi) >> 1;
-    if (offs[mid] <= row) lo = mid; else hi = mid;
-  }
-  return lo;
-}
-
 // One warp per output row.  SILU=false: x row gathered through src_row; SILU=true: row = [gate | up].
 template <bool SILU>
 __global__ void __launch_bounds__(256) quant_rows_kernel(const __half* __restrict__ x, int H, int64_t in_pitch,
@@ -202,88 +157,17 @@ __global__ void __launch_bounds__(256) quant_rows_kernel(const __half* __restric
   if (row >= n_rows) return;
   int a_bits = actq[0].x, gsize = actq[0].y;
   if (E > 1) {
-    int e = find_expert(expert_offsets, E, row);
+    if (row >= expert_offsets[E]) return;  // rows past the last expert are not owned by anyone
+    const int e = find_expert(expert_offsets, E, row);
     a_bits = actq[e].x;
     gsize = actq[e].y;
-    if (row >= expert_offsets[E]) return;  // rows past the last expert are not owned by anyone
   }
   const int64_t srow = src_row ? src_row[row] : row;
   const __half* in = x + srow * in_pitch;
-  const int n8 = H >> 3;
-
-  if (a_bits >= 16) {
-    __half* o = out_f16 + static_cast<int64_t>(row) * H;
-    for (int i = lane; i < n8; i += 32) {
-      float v[8];
-      load8<SILU>(in, H, i, v);
-      uint4 pk;
-      __half2* ph = reinterpret_cast<__half2*>(&pk);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) ph[j] = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
-      *reinterpret_cast<uint4*>(o + i * 8) = pk;
-    }
-    return;
-  }
-  const float upper = static_cast<float>((1 << (a_bits - 1)) - 1);
-  int8_t* o = out_q8 + static_cast<int64_t>(row) * H;
-  __half* so = scales + static_cast<int64_t>(row) * scale_cols;
-
-  if (gsize <= 0) {
-    float amax = 0.f;
-    for (int i = lane; i < n8; i += 32) {
-      float v[8];
-      load8<SILU>(in, H, i, v);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
-    }
-    amax = warp_max(amax);
-    __half sh = __float2half_rn(__fdiv_rn(amax, upper));
-    if (__half2float(sh) == 0.f) sh = __float2half(1.f);
-    const float sf = __half2float(sh);
-    if (lane == 0) so[0] = sh;
-    for (int i = lane; i < n8; i += 32) {
-      float v[8];
-      load8<SILU>(in, H, i, v);
-      uint2 pk;
-      int8_t* pb = reinterpret_cast<int8_t*>(&pk);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float q = h_round(__fdiv_rn(v[j], sf));
-        q = rintf(fminf(fmaxf(q, -upper), upper));
-        pb[j] = static_cast<int8_t>(static_cast<int>(q));
-      }
-      *reinterpret_cast<uint2*>(o + i * 8) = pk;
-    }
-  } else {
-    // gsize == 128: 16 lanes (16 x 8 elements) per group
-    const int iters = (n8 + 31) / 32;
-    for (int it = 0; it < iters; ++it) {
-      const int i = it * 32 + lane;
-      float v[8];
-      float amax = 0.f;
-      if (i < n8) {
-        load8<SILU>(in, H, i, v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
-      }
-      amax = half_warp_max(amax);
-      __half sh = __float2half_rn(__fdiv_rn(amax, upper));
-      if (__half2float(sh) == 0.f) sh = __float2half(1.f);
-      const float sf = __half2float(sh);
-      if (i < n8) {
-        if ((lane & 15) == 0) so[i >> 4] = sh;
-        uint2 pk;
-        int8_t* pb = reinterpret_cast<int8_t*>(&pk);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float q = h_round(__fdiv_rn(v[j], sf));
-          q = rintf(fminf(fmaxf(q, -upper), upper));
-          pb[j] = static_cast<int8_t>(static_cast<int>(q));
-        }
-        *reinterpret_cast<uint2*>(o + i * 8) = pk;
-      }
-    }
-  }
+  auto ld = [&](int i, float (&v)[8]) { load8<SILU>(in, H, i, v); };
+  quantize_row(ld, H, lane, a_bits, gsize, out_q8 ? out_q8 + static_cast<int64_t>(row) * H : nullptr,
+               out_f16 ? out_f16 + static_cast<int64_t>(row) * H : nullptr,
+               scales ? scales + static_cast<int64_t>(row) * scale_cols : nullptr);
 }
 }  // namespace
 

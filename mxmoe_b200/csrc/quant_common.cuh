@@ -1,0 +1,134 @@
+// Per-token activation quantization shared by the plain (moe_ops.cu) and Hadamard (hadamard.cu) kernels.
+// Numerics: quant_minmax (mxmoe/quant/quant.py:40-84) on an fp16 tensor, symmetric, clip=(1,1), every
+// operation rounded to fp16 the way torch does for half tensors, plus the scale==0 -> 1 guard of the
+// reference kernel (mxmoe/kernels/src/include/quantize.cuh:256).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mxb {
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float half_warp_max(float v) {  // reduce inside each group of 16 lanes
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float h_round(float x) { return __half2float(__float2half_rn(x)); }
+
+// act_fn(gate) * up on fp16 tensors: silu evaluated in fp32 and rounded to fp16, product rounded to fp16
+__device__ __forceinline__ float silu_mul_h(__half g, __half u) {
+  float gf = __half2float(g);
+  float s = h_round(__fdiv_rn(gf, 1.f + expf(-gf)));
+  return h_round(s * __half2float(u));
+}
+
+template <bool SILU>
+__device__ __forceinline__ void load8(const __half* __restrict__ row, int H, int idx8, float (&x)[8]) {
+  if (SILU) {
+    uint4 g = *reinterpret_cast<const uint4*>(row + idx8 * 8);
+    uint4 u = *reinterpret_cast<const uint4*>(row + H + idx8 * 8);
+    const __half* gh = reinterpret_cast<const __half*>(&g);
+    const __half* uh = reinterpret_cast<const __half*>(&u);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] = silu_mul_h(gh[j], uh[j]);
+  } else {
+    uint4 v = *reinterpret_cast<const uint4*>(row + idx8 * 8);
+    const __half* vh = reinterpret_cast<const __half*>(&v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] = __half2float(vh[j]);
+  }
+}
+
+__device__ __forceinline__ int find_expert(const int32_t* __restrict__ offs, int E, int row) {
+  int lo = 0, hi = E;  // largest e with offs[e] <= row
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (offs[mid] <= row) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__device__ __forceinline__ uint2 quant8(const float (&v)[8], float sf, float upper) {
+  uint2 pk;
+  int8_t* pb = reinterpret_cast<int8_t*>(&pk);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float q = h_round(__fdiv_rn(v[j], sf));
+    q = rintf(fminf(fmaxf(q, -upper), upper));
+    pb[j] = static_cast<int8_t>(static_cast<int>(q));
+  }
+  return pk;
+}
+__device__ __forceinline__ __half make_scale(float amax, float upper) {
+  __half sh = __float2half_rn(__fdiv_rn(amax, upper));
+  if (__half2float(sh) == 0.f) sh = __float2half(1.f);
+  return sh;
+}
+
+// One warp quantizes one row of H values delivered 8 at a time by `ld(idx8, v)`.
+// a_bits 16: fp16 copy to o_f16; 8 / 4: int8 containers to o_q8 with scale(s) to so.
+template <typename Loader>
+__device__ __forceinline__ void quantize_row(Loader ld, int H, int lane, int a_bits, int gsize, int8_t* __restrict__ o_q8,
+                                             __half* __restrict__ o_f16, __half* __restrict__ so) {
+  const int n8 = H >> 3;
+  if (a_bits >= 16) {
+    for (int i = lane; i < n8; i += 32) {
+      float v[8];
+      ld(i, v);
+      uint4 pk;
+      __half2* ph = reinterpret_cast<__half2*>(&pk);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ph[j] = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
+      *reinterpret_cast<uint4*>(o_f16 + i * 8) = pk;
+    }
+    return;
+  }
+  const float upper = static_cast<float>((1 << (a_bits - 1)) - 1);
+  if (gsize <= 0) {
+    float amax = 0.f;
+    for (int i = lane; i < n8; i += 32) {
+      float v[8];
+      ld(i, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
+    }
+    amax = warp_max(amax);
+    const __half sh = make_scale(amax, upper);
+    const float sf = __half2float(sh);
+    if (lane == 0) so[0] = sh;
+    for (int i = lane; i < n8; i += 32) {
+      float v[8];
+      ld(i, v);
+      *reinterpret_cast<uint2*>(o_q8 + i * 8) = quant8(v, sf, upper);
+    }
+  } else {  // gsize == 128: 16 lanes x 8 elements per group
+    const int iters = (n8 + 31) / 32;
+    for (int it = 0; it < iters; ++it) {
+      const int i = it * 32 + lane;
+      float v[8];
+      float amax = 0.f;
+      if (i < n8) {
+        ld(i, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(v[j]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = 0.f;
+      }
+      amax = half_warp_max(amax);
+      const __half sh = make_scale(amax, upper);
+      if (i < n8) {
+        if ((lane & 15) == 0) so[i >> 4] = sh;
+        *reinterpret_cast<uint2*>(o_q8 + i * 8) = quant8(v, __half2float(sh), upper);
+      }
+    }
+  }
+}
+
+}  // namespace mxb

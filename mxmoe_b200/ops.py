@@ -1,0 +1,267 @@
+"""ctypes binding of libmxmoe_b200.so (include/mxmoe_b200.h) and the host-side mirror of the
+reference's operator module.
+
+The reference's (dead) pybind module `mxmoe_ops` (mxmoe/kernels/src/ref_bind.cu:759-766) exposes
+`quant_inp_act`, `gg_mxmoe_share_fused` and `silu_mul_then_quant` with
+`qparams_per_exp: list[tuple(a_bits, w_bits, gsize, sym)]`; the functions of the same names below keep
+that argument meaning.  PyTorch is used only for device memory and streams: every call passes
+`tensor.data_ptr()` and the current CUDA stream to the C-ABI.  There is NO CPU fallback: if the
+shared library is missing or the device is not sm_100 the import of a symbol / creation of the
+handle raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmxmoe_b200.so")
+
+
+class MxbError(RuntimeError):
+    pass
+
+
+class MxbProblem(C.Structure):
+    _fields_ = [
+        ("A", C.c_void_p), ("B", C.c_void_p), ("scale_a", C.c_void_p), ("scale_b", C.c_void_p),
+        ("C", C.c_void_p), ("m_range", C.c_void_p),
+        ("lda", C.c_int64), ("ldc", C.c_int64),
+        ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
+        ("a_bits", C.c_int32), ("w_bits", C.c_int32), ("gsize", C.c_int32), ("sym", C.c_int32),
+        ("tile_n", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class MxbActQ(C.Structure):
+    _fields_ = [("a_bits", C.c_int32), ("gsize", C.c_int32)]
+
+
+class MxbTileChoice(C.Structure):
+    _fields_ = [("tile_m", C.c_int32), ("tile_n", C.c_int32), ("tile_k", C.c_int32), ("stages", C.c_int32),
+                ("path", C.c_int32), ("est_us", C.c_float)]
+
+
+# every symbol include/mxmoe_b200.h declares: (name, restype, argtypes)
+_P, _I, _I64 = C.c_void_p, C.c_int, C.c_int64
+EXPORTS = [
+    ("mxb_create", _I, [_I, C.POINTER(_P)]),
+    ("mxb_destroy", _I, [_P]),
+    ("mxb_last_error", C.c_char_p, []),
+    ("mxb_sm_count", _I, [_P]),
+    ("mxb_version", C.c_char_p, []),
+    ("mxb_group_gemm", _I, [_P, C.POINTER(MxbProblem), _I, _P]),
+    ("mxb_group_gemm_debug_acc", _I, [_P, C.POINTER(MxbProblem), _I, C.POINTER(_P), _P]),
+    ("mxb_group_gemm_reflayout", _I, [_P] + [_P] * 14 + [_I, _P]),
+    ("mxb_permute", _I, [_P, _P, _I, _I, _I, _P, _P, _P, _P]),
+    ("mxb_quant_act", _I, [_P, _P, _I, _P, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),
+    ("mxb_silu_mul_quant", _I, [_P, _P, _I, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),
+    ("mxb_combine", _I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _P]),
+    ("mxb_quant_pack_weight", _I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    ("mxb_repack_from_ref", _I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    ("mxb_packed_bytes", _I64, [_I, _I, _I]),
+    ("mxb_scale_elems", _I64, [_I, _I, _I, _I, _I, _I]),
+    ("mxb_select_tiles", _I, [_P, C.POINTER(MxbProblem), _I, C.POINTER(MxbTileChoice)]),
+]
+
+_lib = None
+
+
+def load_library(path: str = _LIB_PATH):
+    """dlopen the C-ABI library and bind every export; raises if it is missing (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise MxbError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(make -C mxmoe_b200/csrc). mxmoe_b200 has no CPU or PyTorch fallback.")
+    lib = C.CDLL(path)
+    for name, res, args in EXPORTS:
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+@dataclass
+class Problem:
+    """One GroupGEMM problem in native operand layouts (see include/mxmoe_b200.h)."""
+    A: torch.Tensor
+    B: torch.Tensor
+    C: torch.Tensor
+    M: int
+    N: int
+    K: int
+    w_bits: int = 16
+    a_bits: int = 16
+    gsize: int = -1
+    sym: bool = True
+    scale_a: Optional[torch.Tensor] = None
+    scale_b: Optional[torch.Tensor] = None
+    m_range: Optional[torch.Tensor] = None  # device int32 view of {row_begin,row_end}
+    lda: int = 0
+    ldc: int = 0
+    tile_n: int = 0
+
+    def to_c(self) -> MxbProblem:
+        return MxbProblem(_ptr(self.A), _ptr(self.B), _ptr(self.scale_a), _ptr(self.scale_b), _ptr(self.C),
+                          _ptr(self.m_range), self.lda, self.ldc, self.M, self.N, self.K, self.a_bits, self.w_bits,
+                          self.gsize, 1 if self.sym else 0, self.tile_n, 0)
+
+
+class Handle:
+    """mxb_handle_t owner.  One per (device, stream-of-use)."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        if not torch.cuda.is_available():
+            raise MxbError("mxmoe_b200 needs a CUDA device (sm_100); there is no CPU path")
+        h = C.c_void_p()
+        rc = self.lib.mxb_create(device, C.byref(h))
+        if rc != 0:
+            raise MxbError(f"mxb_create failed ({rc}): {self.lib.mxb_last_error().decode()}")
+        self.h = h
+        self.device = device
+        self._keep = {}
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.mxb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            raise MxbError(f"{what} failed ({rc}): {self.lib.mxb_last_error().decode()}")
+
+    @property
+    def sm_count(self) -> int:
+        return self.lib.mxb_sm_count(self.h)
+
+    # ---------------------------------------------------------------- grouped GEMM
+    def pack_problems(self, problems: Sequence[Problem]):
+        """Build the ctypes array once; reuse it across calls to hit the plan cache without re-marshalling."""
+        arr = (MxbProblem * len(problems))(*[p.to_c() for p in problems])
+        return arr
+
+    def group_gemm(self, problems, acc_out: Optional[Sequence[Optional[torch.Tensor]]] = None):
+        arr = problems if isinstance(problems, C.Array) else self.pack_problems(problems)
+        n = len(arr)
+        if acc_out is None:
+            rc = self.lib.mxb_group_gemm(self.h, arr, n, _stream())
+        else:
+            ptrs = (C.c_void_p * n)(*[_ptr(t) for t in acc_out])
+            rc = self.lib.mxb_group_gemm_debug_acc(self.h, arr, n, ptrs, _stream())
+        self._check(rc, "mxb_group_gemm")
+
+    def select_tiles(self, problems: Sequence[Problem]) -> List[MxbTileChoice]:
+        arr = self.pack_problems(problems)
+        out = (MxbTileChoice * len(arr))()
+        self._check(self.lib.mxb_select_tiles(self.h, arr, len(arr), out), "mxb_select_tiles")
+        return list(out)
+
+    # ---------------------------------------------------------------- MoE pieces
+    def permute(self, topk_ids: torch.Tensor, E: int):
+        T, k = topk_ids.shape
+        dev = topk_ids.device
+        ids = topk_ids.to(torch.int32).contiguous()
+        offs = torch.empty(E + 1, dtype=torch.int32, device=dev)
+        src = torch.empty(T * k, dtype=torch.int32, device=dev)
+        slot = torch.empty(T, k, dtype=torch.int32, device=dev)
+        self._check(self.lib.mxb_permute(self.h, _ptr(ids), T, k, E, _ptr(offs), _ptr(src), _ptr(slot), _stream()),
+                    "mxb_permute")
+        return offs, src, slot
+
+    @staticmethod
+    def _actq(actq: Sequence[Tuple[int, int]]):
+        return (MxbActQ * len(actq))(*[MxbActQ(a, g) for a, g in actq])
+
+    def quant_act(self, x, src_row, n_rows, expert_offsets, actq, hadamard=False, out_q8=None, out_f16=None,
+                  scales=None):
+        H = x.shape[-1]
+        dev = x.device
+        any_q = any(a < 16 for a, _ in actq)
+        any_f = any(a >= 16 for a, _ in actq)
+        cols = H // 128 if any(a < 16 and g == 128 for a, g in actq) else 1
+        if any_q and out_q8 is None:
+            out_q8 = torch.empty(n_rows, H, dtype=torch.int8, device=dev)
+        if any_q and scales is None:
+            scales = torch.empty(n_rows, cols, dtype=torch.float16, device=dev)
+        if any_f and out_f16 is None:
+            out_f16 = torch.empty(n_rows, H, dtype=torch.float16, device=dev)
+        self._check(self.lib.mxb_quant_act(self.h, _ptr(x), H, _ptr(src_row), n_rows, _ptr(expert_offsets),
+                                           self._actq(actq), len(actq), int(hadamard), _ptr(out_q8), _ptr(out_f16),
+                                           _ptr(scales), cols, _stream()), "mxb_quant_act")
+        return out_q8, out_f16, scales
+
+    def silu_mul_quant(self, gate_up, n_rows, expert_offsets, actq, hadamard=False, out_q8=None, out_f16=None,
+                       scales=None):
+        I = gate_up.shape[-1] // 2
+        dev = gate_up.device
+        any_q = any(a < 16 for a, _ in actq)
+        any_f = any(a >= 16 for a, _ in actq)
+        cols = I // 128 if any(a < 16 and g == 128 for a, g in actq) else 1
+        if any_q and out_q8 is None:
+            out_q8 = torch.empty(n_rows, I, dtype=torch.int8, device=dev)
+        if any_q and scales is None:
+            scales = torch.empty(n_rows, cols, dtype=torch.float16, device=dev)
+        if any_f and out_f16 is None:
+            out_f16 = torch.empty(n_rows, I, dtype=torch.float16, device=dev)
+        self._check(self.lib.mxb_silu_mul_quant(self.h, _ptr(gate_up), I, n_rows, _ptr(expert_offsets),
+                                                self._actq(actq), len(actq), int(hadamard), _ptr(out_q8),
+                                                _ptr(out_f16), _ptr(scales), cols, _stream()), "mxb_silu_mul_quant")
+        return out_q8, out_f16, scales
+
+    def combine(self, down_out, slot_of, topk_w, shared_out=None, out=None):
+        T, k = slot_of.shape
+        H = down_out.shape[-1]
+        if out is None:
+            out = torch.empty(T, H, dtype=torch.float16, device=down_out.device)
+        self._check(self.lib.mxb_combine(self.h, _ptr(down_out), H, _ptr(slot_of), _ptr(topk_w), T, k, _ptr(shared_out),
+                                         _ptr(out), _stream()), "mxb_combine")
+        return out
+
+    # ---------------------------------------------------------------- offline weights
+    def quant_pack_weight(self, W: torch.Tensor, w_bits: int, a_bits: int, gsize: int, sym: bool):
+        """fp16 [N,K] -> (packed uint8 native layout, scales fp16 group-major).  quantize.cuh:218-475 numerics."""
+        N, K = W.shape
+        W = W.contiguous()
+        packed = torch.empty(self.lib.mxb_packed_bytes(N, K, w_bits), dtype=torch.uint8, device=W.device)
+        ne = self.lib.mxb_scale_elems(N, K, w_bits, a_bits, gsize, int(sym))
+        scales = torch.empty(ne, dtype=torch.float16, device=W.device)
+        self._check(self.lib.mxb_quant_pack_weight(self.h, _ptr(W), N, K, w_bits, a_bits, gsize, int(sym), _ptr(packed),
+                                                   _ptr(scales), _stream()), "mxb_quant_pack_weight")
+        return packed.view(N, K * w_bits // 8), scales
+
+    def repack_from_ref(self, ref_packed: torch.Tensor, N: int, K: int, w_bits: int, a_bits: int, sym: bool):
+        packed = torch.empty(N, K * w_bits // 8, dtype=torch.uint8, device=ref_packed.device)
+        self._check(self.lib.mxb_repack_from_ref(self.h, _ptr(ref_packed), N, K, w_bits, a_bits, int(sym), _ptr(packed),
+                                                 _stream()), "mxb_repack_from_ref")
+        return packed
+
+
+_default: Optional[Handle] = None
+
+
+def default_handle() -> Handle:
+    global _default
+    if _default is None:
+        _default = Handle(torch.cuda.current_device())
+    return _default

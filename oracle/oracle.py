@@ -236,6 +236,18 @@ def pack_weightonly_native(q: np.ndarray, bits: int, sym: bool) -> np.ndarray:
     return word.view(np.uint8).reshape(N, K // 2)
 
 
+def pack_wxax_native(q: np.ndarray, bits: int) -> np.ndarray:
+    """Native (B200) WxAx weight layout: 8-bit = int8 two's complement [N,K] in K order; 4-bit =
+    [N,K/2] bytes, inside every 32-k block byte j holds k=j in the low and k=j+16 in the high nibble
+    (two's complement), so the in-smem unpack is one shift/mask per 32-bit word."""
+    N, K = q.shape
+    if bits == 8:
+        return q.astype(np.int8).view(np.uint8)
+    assert bits == 4 and K % 32 == 0
+    u = (q.astype(np.int64) & 0xF).astype(np.uint8).reshape(N, K // 32, 2, 16)
+    return (u[:, :, 0, :] | (u[:, :, 1, :] << np.uint8(4))).reshape(N, K // 2)
+
+
 # --------------------------------------------------------------------------- GEMM problems
 def gemm_fp16(A: np.ndarray, W: np.ndarray) -> np.ndarray:
     """cta_gemm.cuh:8-107: fp16 operands, fp32 accumulate, one rounding to fp16."""
@@ -261,7 +273,8 @@ def gemm_wxax(qA, sA, qW, sW, gsize: int):
         acc[i] = np.rint(a @ w.T).astype(np.int32)          # exact: |sum| < 2^53
         prod = (sA[:, i:i + 1].astype(f16) * sW[:, i].astype(f16)[None, :]).astype(f16)
         # fused multiply-add in fp32 (nvcc contracts `out += float(acc) * float(prod)`)
-        out = (acc[i].astype(f64) * prod.astype(f64) + out.astype(f64)).astype(f32)
+        # float(acc) rounds to fp32 first (|acc| can exceed 2^24), then one fp32 FMA
+        out = (acc[i].astype(f32).astype(f64) * prod.astype(f64) + out.astype(f64)).astype(f32)
     return acc, out.astype(f16)
 
 
