@@ -1,0 +1,183 @@
+"""Parity of the permute / act-quant (+Hadamard) / silu-mul-quant / combine / weight-pack kernels
+(through the C-ABI) against the CPU oracle.  Integer and index outputs: bit-exact.  Paths that go
+through a transcendental (silu) or an fp32 butterfly (Hadamard) may land on the other side of an
+fp16 rounding boundary in rare elements: the test states the tolerance where that applies."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def H():
+    from mxmoe_b200 import ops
+    return ops.Handle(0)
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def rand16(rng, *shape, scale=1.0):
+    return ((rng.random(shape) * 2 - 1) * scale).astype(np.float16)
+
+
+@pytest.mark.parametrize("T,k,E", [(1, 1, 1), (37, 4, 12), (512, 4, 60), (8192, 4, 60), (300, 6, 64), (5000, 8, 64), (64, 2, 8)])
+def test_permute_bit_exact(H, T, k, E):
+    rng = np.random.default_rng(T + E)
+    ids = np.stack([rng.permutation(E)[:k] for _ in range(T)]).astype(np.int32)
+    offs, src, slot = H.permute(dev(ids), E)
+    torch.cuda.synchronize()
+    r_offs, r_src, r_slot = O.permute(ids, E)
+    assert np.array_equal(offs.cpu().numpy(), r_offs)
+    assert np.array_equal(src.cpu().numpy(), r_src)
+    assert np.array_equal(slot.cpu().numpy(), r_slot)
+    # second call re-uses the workspace ticket
+    offs2, _, _ = H.permute(dev(ids), E)
+    assert np.array_equal(offs2.cpu().numpy(), r_offs)
+
+
+def test_permute_skewed_and_empty_experts(H):
+    rng = np.random.default_rng(3)
+    T, k, E = 4096, 2, 16
+    ids = rng.choice([0, 3, 15], size=(T, k)).astype(np.int32)  # 13 experts get nothing, collisions inside a token allowed
+    offs, src, slot = H.permute(dev(ids), E)
+    r = O.permute(ids, E)
+    assert np.array_equal(offs.cpu().numpy(), r[0]) and np.array_equal(src.cpu().numpy(), r[1]) and np.array_equal(slot.cpu().numpy(), r[2])
+
+
+@pytest.mark.parametrize("Hdim", [2048, 1408, 256, 4096])
+def test_quant_act_mixed_experts_bit_exact(H, Hdim):
+    rng = np.random.default_rng(Hdim)
+    T, k, E = 96, 2, 6
+    x = rand16(rng, T, Hdim, scale=3.0)
+    x[5] = 0  # all-zero token: scale guard (quantize.cuh:256)
+    ids = np.stack([rng.permutation(E)[:k] for _ in range(T)]).astype(np.int32)
+    offs, src, _ = O.permute(ids, E)
+    actq = [(8, -1), (4, -1), (16, -1), (4, 128), (8, 128), (4, -1)]
+    q8, f16, sc = H.quant_act(dev(x), dev(src), T * k, dev(offs), actq)
+    torch.cuda.synchronize()
+    q8, f16, sc = q8.cpu().numpy(), f16.cpu().numpy(), sc.cpu().numpy()
+    xs = x[src]
+    for e, (a, g) in enumerate(actq):
+        rows = slice(offs[e], offs[e + 1])
+        if a == 16:
+            assert np.array_equal(f16[rows].view(np.uint16), xs[rows].view(np.uint16))
+            continue
+        rq, rs = O.quant_act(xs[rows], a, g)
+        assert np.array_equal(q8[rows].astype(np.int32), rq), f"expert {e} q"
+        assert np.array_equal(sc[rows, :rs.shape[1]].view(np.uint16), rs.view(np.uint16)), f"expert {e} scale"
+
+
+def test_silu_mul_quant(H):
+    rng = np.random.default_rng(11)
+    rows, I = 200, 1408
+    gu = rand16(rng, rows, 2 * I, scale=4.0)
+    offs = np.array([0, 50, 50, 120, 200], np.int32)
+    actq = [(8, -1), (4, -1), (4, -1), (16, -1)]
+    q8, f16, sc = H.silu_mul_quant(dev(gu), rows, dev(offs), actq)
+    torch.cuda.synchronize()
+    q8, f16, sc = q8.cpu().numpy(), f16.cpu().numpy(), sc.cpu().numpy()
+    h = O.silu_mul(gu)
+    # expf on the device vs numpy exp: identical after the fp16 rounding except at rounding boundaries
+    got = f16[120:200].astype(np.float32)
+    ref = h[120:200].astype(np.float32)
+    assert np.mean(got != ref) < 2e-3 and np.abs(got - ref).max() <= 2 ** -8 * np.abs(ref).max()
+    for e, (a, g) in enumerate(actq[:3]):
+        r = slice(offs[e], offs[e + 1])
+        if offs[e] == offs[e + 1]:
+            continue
+        rq, rs = O.quant_act(h[r], a, g)
+        # tolerance: a 1-ulp difference in h can move a code by one step and, if it is the row maximum, the scale by 1 ulp
+        assert np.mean(q8[r].astype(np.int32) != rq) < 5e-3
+        assert np.abs(q8[r].astype(np.int32) - rq).max() <= 1
+        assert np.abs(sc[r, 0].astype(np.float32) - rs[:, 0].astype(np.float32)).max() <= 2 ** -10 * np.abs(rs.astype(np.float32)).max()
+
+
+@pytest.mark.parametrize("n", [2048, 1408, 5632, 2560, 256, 96])
+def test_hadamard_quant_fp16_passthrough(H, n):
+    """hadamard=1 with a_bits=16 returns the rotated row itself: compare with hadamard_f16 (hadamard_utils.py:96-105).
+    Tolerance: fp32 butterflies vs float64 oracle -> the fp16 results may differ by one ulp in rare elements."""
+    rng = np.random.default_rng(n)
+    rows = 40
+    x = rand16(rng, rows, n, scale=2.0)
+    x[3, 7] = 40.0  # an outlier the rotation spreads
+    _, f16, _ = H.quant_act(dev(x), None, rows, None, [(16, -1)], hadamard=True)
+    torch.cuda.synchronize()
+    got = f16.cpu().numpy().astype(np.float64)
+    ref = O.hadamard_f16(x).astype(np.float64)
+    scale = np.abs(ref).max()
+    assert np.abs(got - ref).max() <= 2e-3 * scale
+    assert np.mean(got != ref) < 0.02
+    # orthogonality: energy is preserved
+    np.testing.assert_allclose((got ** 2).sum(1), (x.astype(np.float64) ** 2).sum(1), rtol=5e-3)
+
+
+def test_hadamard_silu_quant_close_to_oracle(H):
+    rng = np.random.default_rng(2)
+    rows, I = 64, 1408
+    gu = rand16(rng, rows, 2 * I, scale=3.0)
+    q8, _, sc = H.silu_mul_quant(dev(gu), rows, None, [(8, -1)], hadamard=True)
+    torch.cuda.synchronize()
+    h = O.hadamard_f16(O.silu_mul(gu))
+    rq, rs = O.quant_act(h, 8, -1)
+    deq = q8.cpu().numpy().astype(np.float32) * sc.cpu().numpy().astype(np.float32)
+    rdeq = rq.astype(np.float32) * rs.astype(np.float32)
+    # dequantized rows agree to one quantization step
+    assert np.abs(deq - rdeq).max() <= 1.01 * rs.astype(np.float32).max()
+    assert np.mean(q8.cpu().numpy().astype(np.int32) != rq) < 0.02
+
+
+def test_combine_bit_exact(H):
+    rng = np.random.default_rng(4)
+    T, k, E, Hd = 333, 4, 12, 2048
+    ids = np.stack([rng.permutation(E)[:k] for _ in range(T)]).astype(np.int32)
+    _, _, slot = O.permute(ids, E)
+    down = rand16(rng, T * k, Hd, scale=2.0)
+    w = rng.random((T, k)).astype(np.float32)
+    shared = rand16(rng, T, Hd)
+    out = H.combine(dev(down), dev(slot), dev(w), dev(shared))
+    out2 = H.combine(dev(down), dev(slot), dev(w))
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint16), O.combine(down, slot, w, shared).view(np.uint16))
+    assert np.array_equal(out2.cpu().numpy().view(np.uint16), O.combine(down, slot, w).view(np.uint16))
+
+
+@pytest.mark.parametrize("w_bits,a_bits,gsize,sym", [(8, 8, -1, True), (4, 4, -1, True), (4, 4, 128, True), (4, 16, 128, False),
+                                                     (4, 16, -1, True), (8, 16, 128, True), (8, 16, -1, False), (4, 16, 128, True)])
+def test_quant_pack_weight_bit_exact(H, w_bits, a_bits, gsize, sym):
+    rng = np.random.default_rng(w_bits + a_bits)
+    N, K = 96, 512
+    W = rand16(rng, N, K)
+    W[7] = 0
+    packed, scales = H.quant_pack_weight(dev(W), w_bits, a_bits, gsize, sym)
+    torch.cuda.synchronize()
+    q, s, z = O.quant_weight(W, w_bits, gsize, sym)
+    ref_p = O.pack_wxax_native(q, w_bits) if a_bits < 16 else O.pack_weightonly_native(q, w_bits, sym)
+    ref_s = O.permute_scale(s, None if sym else z, sym)
+    assert np.array_equal(packed.cpu().numpy(), ref_p.reshape(N, -1))
+    assert np.array_equal(scales.cpu().numpy().view(np.uint16), ref_s.reshape(-1).view(np.uint16))
+
+
+@pytest.mark.parametrize("w_bits,a_bits,sym", [(8, 8, True), (4, 4, True), (4, 16, False), (4, 16, True), (8, 16, True)])
+def test_repack_from_reference_layout(H, w_bits, a_bits, sym):
+    """Weights packed by the reference's own packers (oracle restatement pinned to oracle/_ref/ref_pack) load
+    into the native layout bit-identically."""
+    rng = np.random.default_rng(w_bits * 3 + a_bits)
+    N, K = 64, 256
+    if a_bits < 16:
+        hi = (1 << (w_bits - 1)) - 1
+        q = rng.integers(-hi, hi + 1, (N, K)).astype(np.int32)
+        ref_packed = O.pack_wxax(q, w_bits)
+        want = O.pack_wxax_native(q, w_bits)
+    else:
+        hi = (1 << (w_bits - 1)) - 1
+        q = rng.integers(-hi, hi + 1, (N, K)).astype(np.int32) if sym else rng.integers(0, 1 << w_bits, (N, K)).astype(np.int32)
+        ref_packed = O.pack_weightonly_ref(q, w_bits, sym)
+        want = O.pack_weightonly_native(q, w_bits, sym)
+    got = H.repack_from_ref(dev(ref_packed), N, K, w_bits, a_bits, sym)
+    torch.cuda.synchronize()
+    assert np.array_equal(got.cpu().numpy(), want.reshape(N, -1))
