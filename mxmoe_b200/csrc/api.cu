@@ -160,6 +160,11 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, mxb
   if (p.N % 8 != 0) return fail(MXB_EINVAL, "N=%d must be a multiple of 8", p.N);
   if (p.K % 32 != 0) return fail(MXB_EINVAL, "K=%d must be a multiple of 32", p.K);
   if (p.gsize == 128 && p.K % 128 != 0) return fail(MXB_EINVAL, "K=%d must be a multiple of the group size 128", p.K);
+  if (p.M == 0 && !p.m_range) {  // empty problem (the reference's callers skip these, ref_bind.cu:360): zero tiles
+    d->n_tiles = 1;
+    d->bn = 32;
+    return MXB_OK;
+  }
   if (!p.A || !p.B || !p.C) return fail(MXB_EINVAL, "null operand pointer");
   if (k.epi != mxb::EPI_F32 && (!p.scale_a || !p.scale_b)) return fail(MXB_EINVAL, "quantized problem without scales");
   if (k.conv >= mxb::CONV_W4_F16 && !p.scale_b) return fail(MXB_EINVAL, "weight-only problem without scale_b");

@@ -1,0 +1,183 @@
+"""The MoE-layer hot path as one object: permute -> per-token act-quant -> mixed-precision GroupGEMM (gate_up)
+-> silu*mul (+online Hadamard) + quant -> GroupGEMM (down) -> top-k weighted combine.
+
+This is the composition the reference intends with quant_inp_act -> gg_mxmoe_share_fused ->
+silu_mul_then_quant -> gg_mxmoe_share_fused (mxmoe/kernels/src/ref_bind.cu:312-757) plus the combine it
+lacks (ref_bind.cu:66).  Differences by design: no host synchronisation anywhere (the per-expert token
+counts stay on the device and the GEMM kernel reads them through MxbProblem.m_range), problem lists are
+marshalled once and re-used through the plan cache, shared experts ride in the same launches.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import ops
+from .config import QExpertConfig, QLayerConfig, QLinearConfig
+
+
+@dataclass
+class ExpertWeights:
+    """Packed weights of one expert (index E = the fused shared expert)."""
+    gu_packed: torch.Tensor   # gate_up [2I', H] in the native layout of its qconfig
+    gu_scale: Optional[torch.Tensor]
+    dn_packed: torch.Tensor   # down [H, I']
+    dn_scale: Optional[torch.Tensor]
+    q_gu: QLinearConfig
+    q_dn: QLinearConfig
+
+
+def _check_tied(q: QExpertConfig):
+    g, u = q.gate, q.up
+    if (g.w_bits, g.a_bits, g.w_gsize, g.w_sym) != (u.w_bits, u.a_bits, u.w_gsize, u.w_sym):
+        raise ValueError("gate and up must share a qconfig (they are one fused GEMM; bits_solver.py:378-379)")
+
+
+class MoELayer:
+    def __init__(self, handle: ops.Handle, E: int, topk: int, H: int, I: int, ns: int, qlayer: QLayerConfig,
+                 max_tokens: int, hadamard_down: bool = False, expert_ids: Optional[Sequence[int]] = None, seed: int = 42,
+                 weights: Optional[dict] = None, device: Optional[torch.device] = None):
+        """expert_ids: the routed experts this rank owns (expert-parallel shard); default all E.
+        weights: optional {expert_idx: (W_gate_up fp16 [2I',H], W_down fp16 [H,I'])}; default U(-1,1) seed 42
+        (the reference bench's distribution, test.cu:877-915)."""
+        self.h = handle
+        self.E, self.topk, self.H, self.I, self.ns = E, topk, H, I, ns
+        self.hadamard_down = hadamard_down
+        self.dev = device or torch.device("cuda", handle.device)
+        self.local_experts = list(expert_ids) if expert_ids is not None else list(range(E))
+        self.EL = len(self.local_experts)
+        self.max_tokens = max_tokens
+        self.experts: List[ExpertWeights] = []
+        gen = torch.Generator(device=self.dev).manual_seed(seed)
+        ids = self.local_experts + ([E] if ns else [])
+        for e in ids:
+            qe = qlayer.experts[str(e)]
+            _check_tied(qe)
+            Ie = I * ns if e == E else I
+            if weights is not None and e in weights:
+                Wgu, Wdn = weights[e]
+                Wgu, Wdn = Wgu.to(self.dev), Wdn.to(self.dev)
+            else:
+                Wgu = torch.rand(2 * Ie, H, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).half()
+                Wdn = torch.rand(H, Ie, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).half()
+            self.experts.append(ExpertWeights(*self._pack(Wgu, qe.gate), *self._pack(Wdn, qe.down), qe.gate, qe.down))
+            del Wgu, Wdn
+        self._alloc(max_tokens)
+        self._build_problems()
+
+    # ------------------------------------------------------------------ setup
+    def _pack(self, W: torch.Tensor, q: QLinearConfig):
+        if q.w_bits == 16:
+            return W.contiguous(), None
+        return self.h.quant_pack_weight(W, q.w_bits, q.a_bits, q.w_gsize, q.w_sym)
+
+    def _alloc(self, T: int):
+        d, H, I, k = self.dev, self.H, self.I, self.topk
+        R = T * k  # routed rows (capacity: every token could land on this rank)
+        f16, i8 = torch.float16, torch.int8
+        qs = [e.q_gu for e in self.experts[:self.EL]] + [e.q_dn for e in self.experts[:self.EL]]
+        any_q = any(q.a_bits < 16 for q in qs)
+        any_f = any(q.a_bits >= 16 for q in qs)
+        g_gu = any(q.a_bits < 16 and q.a_gsize == 128 for q in [e.q_gu for e in self.experts[:self.EL]])
+        g_dn = any(q.a_bits < 16 and q.a_gsize == 128 for q in [e.q_dn for e in self.experts[:self.EL]])
+        self.x_q8 = torch.empty(R, H, dtype=i8, device=d) if any_q else None
+        self.x_f16 = torch.empty(R, H, dtype=f16, device=d) if any_f else None
+        self.x_sc = torch.empty(R, H // 128 if g_gu else 1, dtype=f16, device=d) if any_q else None
+        self.gu_out = torch.empty(R, 2 * I, dtype=f16, device=d)
+        self.h_q8 = torch.empty(R, I, dtype=i8, device=d) if any_q else None
+        self.h_f16 = torch.empty(R, I, dtype=f16, device=d) if any_f else None
+        self.h_sc = torch.empty(R, I // 128 if g_dn else 1, dtype=f16, device=d) if any_q else None
+        self.dn_out = torch.empty(R, H, dtype=f16, device=d)
+        if self.ns:
+            s = self.experts[-1]
+            Is = I * self.ns
+            self.sx_q8 = torch.empty(T, H, dtype=i8, device=d) if s.q_gu.a_bits < 16 else None
+            self.sx_sc = torch.empty(T, H // 128 if s.q_gu.a_gsize == 128 else 1, dtype=f16, device=d) if s.q_gu.a_bits < 16 else None
+            self.s_gu = torch.empty(T, 2 * Is, dtype=f16, device=d)
+            # like the reference workload (gen_workload.py:101) the shared down problem takes the gate config
+            self.sh_q8 = torch.empty(T, Is, dtype=i8, device=d) if s.q_dn.a_bits < 16 else None
+            self.sh_f16 = torch.empty(T, Is, dtype=f16, device=d) if s.q_dn.a_bits >= 16 else None
+            self.sh_sc = torch.empty(T, Is // 128 if s.q_dn.a_gsize == 128 else 1, dtype=f16, device=d) if s.q_dn.a_bits < 16 else None
+            self.s_dn = torch.empty(T, H, dtype=f16, device=d)
+        self.offs = torch.zeros(self.EL + 1, dtype=torch.int32, device=d)
+
+    def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range):
+        A = A_f16 if q.a_bits >= 16 else A_q8
+        return ops.Problem(A, B, C, rows, N, K, q.w_bits, q.a_bits, q.w_gsize, q.w_sym if q.w_bits < 16 else True,
+                           scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range)
+
+    def _build_problems(self):
+        """Marshal the two problem lists once; M of every routed expert is read on the device from self.offs."""
+        H, I, k, T = self.H, self.I, self.topk, self.max_tokens
+        R = T * k
+        gu, dn = [], []
+        for i, ew in enumerate(self.experts[:self.EL]):
+            mr = self.offs[i:i + 2]
+            gu.append(self._problem(ew.q_gu, self.x_q8, self.x_f16, self.x_sc, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * I, H, mr))
+            dn.append(self._problem(ew.q_dn, self.h_q8, self.h_f16, self.h_sc, ew.dn_packed, ew.dn_scale, self.dn_out, R, H, I, mr))
+        self._gu_routed, self._dn_routed = gu, dn
+        self._T_built = None
+
+    def _finalize_problems(self, T: int, x: torch.Tensor):
+        if self._T_built == (T, x.data_ptr()):
+            return
+        gu, dn = list(self._gu_routed), list(self._dn_routed)
+        if self.ns:
+            s = self.experts[-1]
+            Is = self.I * self.ns
+            A_f16 = x if s.q_gu.a_bits >= 16 else None
+            gu.append(self._problem(s.q_gu, self.sx_q8, A_f16, self.sx_sc, s.gu_packed, s.gu_scale, self.s_gu, T, 2 * Is, self.H, None))
+            dn.append(self._problem(s.q_dn, self.sh_q8, self.sh_f16, self.sh_sc, s.dn_packed, s.dn_scale, self.s_dn, T, self.H, Is, None))
+        self._gu_arr = self.h.pack_problems(gu)
+        self._dn_arr = self.h.pack_problems(dn)
+        self._keep = (gu, dn)
+        self._T_built = (T, x.data_ptr())
+
+    # ------------------------------------------------------------------ hot path
+    def actq_gu(self):
+        return [(e.q_gu.a_bits, e.q_gu.a_gsize) for e in self.experts[:self.EL]]
+
+    def actq_dn(self):
+        return [(e.q_dn.a_bits, e.q_dn.a_gsize) for e in self.experts[:self.EL]]
+
+    def forward(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: Optional[torch.Tensor] = None):
+        """x fp16 [T,H]; topk_ids int32 [T,k] in [0,E) (all experts local); topk_w fp32 [T,k] -> fp16 [T,H]."""
+        T = x.shape[0]
+        assert T <= self.max_tokens and self.EL == self.E, "use forward_rows for an expert-parallel shard"
+        h = self.h
+        offs, src, slot = h.permute(topk_ids, self.E)
+        self.offs.copy_(offs)
+        self.run_experts(x, src, T * self.topk, T)
+        return h.combine(self.dn_out, slot, topk_w, self.s_dn if self.ns else None, out)
+
+    def run_experts(self, x: torch.Tensor, src_row: Optional[torch.Tensor], n_rows: int, T_shared: int):
+        """Rows already grouped by local expert (self.offs filled): quant -> gate_up -> silu*mul(+had)+quant -> down.
+        x is gathered through src_row (None: x rows are already in sorted order).  Results land in self.dn_out
+        (routed rows) and self.s_dn (shared expert over the first T_shared rows of x)."""
+        h = self.h
+        self._finalize_problems(T_shared, x)
+        if n_rows > 0 or True:
+            h.quant_act(x, src_row, n_rows, self.offs, self.actq_gu(), False, self.x_q8, self.x_f16, self.x_sc)
+        if self.ns:
+            s = self.experts[-1]
+            if s.q_gu.a_bits < 16:
+                h.quant_act(x, None, T_shared, None, [(s.q_gu.a_bits, s.q_gu.a_gsize)], False, self.sx_q8, None, self.sx_sc)
+        h.group_gemm(self._gu_arr)
+        h.silu_mul_quant(self.gu_out, n_rows, self.offs, self.actq_dn(), self.hadamard_down, self.h_q8, self.h_f16, self.h_sc)
+        if self.ns:
+            s = self.experts[-1]
+            h.silu_mul_quant(self.s_gu, T_shared, None, [(s.q_dn.a_bits, s.q_dn.a_gsize)], self.hadamard_down, self.sh_q8,
+                             self.sh_f16, self.sh_sc)
+        h.group_gemm(self._dn_arr)
+
+    def gemm_ops(self, counts: Sequence[int], T_shared: int) -> int:
+        """sum 2*M*N*K over gate_up + down (+ shared) for the given per-expert token counts (test.cu:109-116)."""
+        tot = 0
+        for m in counts:
+            tot += 2 * m * (2 * self.I) * self.H + 2 * m * self.H * self.I
+        if self.ns:
+            Is = self.I * self.ns
+            tot += 2 * T_shared * (2 * Is) * self.H + 2 * T_shared * self.H * Is
+        return tot

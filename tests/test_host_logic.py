@@ -1,0 +1,70 @@
+"""Host-side logic (JSON contracts, workload generation) against fixtures produced by the reference itself."""
+import json
+import os
+
+import pytest
+
+from mxmoe_b200 import config as C
+from mxmoe_b200 import workload as W
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.mark.parametrize("name,kw", [("fp16", {}), ("qstr", {"qstr": "w4a16_g128_asym"}), ("qcfg", {"qconfig": "file"})])
+def test_workload_matches_reference_generator(name, kw):
+    """generate_workload_from_gate_trace (gen_workload.py:38-110) run by tests/golden/gen_golden.py"""
+    trace = json.load(open(os.path.join(G, "gate_trace.json")))
+    gold = json.load(open(os.path.join(G, "workload.json")))[name]
+    if "qconfig" in kw:
+        kw = {"qconfig": json.load(open(os.path.join(G, "qconfig_mixed.json")))}
+    got = W.generate_workload_from_gate_trace(trace, 8192, 11, **kw)
+    assert got == gold
+
+
+def test_qconfig_json_roundtrip_and_qcfg_list():
+    path = os.path.join(G, "qconfig_mixed.json")
+    qm = C.build_qmodel_cfg_from_json(path)
+    raw = json.load(open(path))
+    assert set(qm.layers) == {"10", "11"} and qm.LT == raw["LT"]
+    e0 = qm.layers["11"].experts["0"]
+    assert e0.gate.to_dict() == {**raw["11"]["experts"]["0"]["gate"], "w_clip": (1.0, 1.0), "a_clip": (1.0, 1.0)}
+    assert str(e0.gate) == f"W{e0.gate.w_bits}A{e0.gate.a_bits}_g-1_sym"
+    assert C.get_qcfg_list(path, 11) == {"w4a4_g-1_sym", "w8a8_g-1_sym"}
+    assert C.QLinearConfig.from_qstr("w4a16_g128_asym").w_sym is False
+    assert C.QLinearConfig.from_qstr(None).qstr() == "fp16"
+    with pytest.raises(ValueError):
+        C.QLinearConfig.from_qstr("w4a16")
+
+
+def test_tile_config_both_schemas(tmp_path):
+    a = {"11": "(TileConfig(BM=128, BN=128, BK=64, WM=64, WN=32, WK=64, STAGE=3, SPLITK=1, MMA='MMA_S8_K32'), "
+               "TileConfig(BM=256, BN=128, BK=128, WM=64, WN=64, WK=128, STAGE=3, SPLITK=1, MMA='MMA_S4_K64'))"}
+    b = {"w8a8_g-1_sym": [{"BM": 128, "BN": 256, "BK": 128, "num_warps": 8}]}
+    pa, pb = tmp_path / "a.json", tmp_path / "b.json"
+    pa.write_text(json.dumps(a)), pb.write_text(json.dumps(b))
+    ta, tb = C.load_tile_config(str(pa)), C.load_tile_config(str(pb))
+    assert [t["BN"] for t in ta["11"]] == [128, 128] and ta["11"][1]["MMA"] == "MMA_S4_K64"
+    assert tb["w8a8_g-1_sym"][0]["BN"] == 256
+
+
+def test_synthetic_traces_and_mixed_qconfig():
+    tr = W.synthetic_gate_trace("qwen2_moe", [11], "fixture")
+    wl = W.generate_workload_from_gate_trace(tr, 8192, 11)
+    ms = [p["shape"][0] for p in wl["layer-11"]["gate_up"]]
+    assert len(ms) == 61 and ms[-1] == 8192 and 32000 < sum(ms[:-1]) <= 32768
+    assert wl["layer-11"]["gate_up"][0]["shape"][1:] == [2816, 2048] and wl["layer-11"]["down"][-1]["shape"] == [8192, 2048, 5632]
+    assert W.workload_ops(wl) == sum(2 * p["shape"][0] * p["shape"][1] * p["shape"][2] for part in ("gate_up", "down") for p in wl["layer-11"][part])
+    for kind in ("uniform", "zipf"):
+        t = W.synthetic_gate_trace("mixtral", [0], kind)
+        assert len(t["layer-0"]["access_freq"]) == 8 and t["num_shared_experts"] == 0
+    q = W.synthetic_mixed_qconfig("qwen2_moe", [11], 5.0)
+    ex = q["11"]["experts"]
+    assert len(ex) == 61 and all(e["gate"] == e["up"] for e in ex.values())
+    tot = w8 = 0
+    for i, e in ex.items():
+        sc = 4 if i == "60" else 1
+        for blk, wt in (("gate", 2), ("down", 1)):
+            tot += wt * sc
+            w8 += wt * sc * (e[blk]["w_bits"] == 8)
+    assert abs(4 + 4 * w8 / tot - 5.0) < 0.1
+    C.qmodel_cfg_from_dict(q)
