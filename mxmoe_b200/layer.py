@@ -38,7 +38,7 @@ def _check_tied(q: QExpertConfig):
 class MoELayer:
     def __init__(self, handle: ops.Handle, E: int, topk: int, H: int, I: int, ns: int, qlayer: QLayerConfig,
                  max_tokens: int, hadamard_down: bool = False, expert_ids: Optional[Sequence[int]] = None, seed: int = 42,
-                 weights: Optional[dict] = None, device: Optional[torch.device] = None):
+                 weights: Optional[dict] = None, device: Optional[torch.device] = None, weight_scale: float = 1.0):
         """expert_ids: the routed experts this rank owns (expert-parallel shard); default all E.
         weights: optional {expert_idx: (W_gate_up fp16 [2I',H], W_down fp16 [H,I'])}; default U(-1,1) seed 42
         (the reference bench's distribution, test.cu:877-915)."""
@@ -60,8 +60,8 @@ class MoELayer:
                 Wgu, Wdn = weights[e]
                 Wgu, Wdn = Wgu.to(self.dev), Wdn.to(self.dev)
             else:
-                Wgu = torch.rand(2 * Ie, H, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).half()
-                Wdn = torch.rand(H, Ie, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).half()
+                Wgu = torch.rand(2 * Ie, H, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).mul_(weight_scale).half()
+                Wdn = torch.rand(H, Ie, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).mul_(weight_scale).half()
             self.experts.append(ExpertWeights(*self._pack(Wgu, qe.gate), *self._pack(Wdn, qe.down), qe.gate, qe.down))
             del Wgu, Wdn
         self._alloc(max_tokens)
@@ -158,7 +158,7 @@ class MoELayer:
         (routed rows) and self.s_dn (shared expert over the first T_shared rows of x)."""
         h = self.h
         self._finalize_problems(T_shared, x)
-        if n_rows > 0 or True:
+        if True:
             h.quant_act(x, src_row, n_rows, self.offs, self.actq_gu(), False, self.x_q8, self.x_f16, self.x_sc)
         if self.ns:
             s = self.experts[-1]
@@ -180,4 +180,26 @@ class MoELayer:
         if self.ns:
             Is = self.I * self.ns
             tot += 2 * T_shared * (2 * Is) * self.H + 2 * T_shared * self.H * Is
+        return tot
+
+    # ------------------------------------------------------------------ bench helpers
+    def gemm_only(self):
+        """Re-issue the two persistent GroupGEMM launches on the buffers of the last forward (kernel timing)."""
+        self.h.group_gemm(self._gu_arr)
+        self.h.group_gemm(self._dn_arr)
+
+    def last_counts(self):
+        o = self.offs.cpu().tolist()
+        return [o[i + 1] - o[i] for i in range(self.EL)]
+
+    def launches_per_step(self) -> int:
+        # permute (2) + act-quant (1 [+1 shared]) + GroupGEMM (1) + silu*mul+quant (1 [+1 shared]) + GroupGEMM (1) + combine (1)
+        return 7 + (2 if self.ns else 0)
+
+    def weight_bytes(self) -> int:
+        tot = 0
+        for e in self.experts:
+            for t in (e.gu_packed, e.gu_scale, e.dn_packed, e.dn_scale):
+                if t is not None:
+                    tot += t.numel() * t.element_size()
         return tot

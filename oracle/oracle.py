@@ -412,3 +412,32 @@ def run_problem(A: np.ndarray, W: np.ndarray, w_bits, a_bits, gsize, sym):
     qa, sa = quant_act(A, a_bits, gsize)
     qw, sw, _ = quant_weight(W, w_bits, gsize, True)
     return gemm_wxax(qa, sa, qw, sw, gsize)[1]
+
+
+# --------------------------------------------------------------------------- whole layer
+def expert_mlp(X, Wgu, Wdn, q_gu, q_dn, hadamard_down: bool):
+    """One expert: gate_up GEMM -> silu*mul -> (online Hadamard on the down input, rotation.py:403-421) -> down GEMM.
+    q_* = (w_bits, a_bits, gsize, sym).  Activations are quantized per token inside run_problem."""
+    gu = run_problem(X, Wgu, *q_gu)
+    h = silu_mul(gu)
+    if hadamard_down:
+        h = hadamard_f16(h)
+    return run_problem(h, Wdn, *q_dn)
+
+
+def moe_layer(x, topk_ids, topk_w, weights, qcfgs, E, hadamard_down=False, shared=None):
+    """The hot path end to end.  weights[e] = (Wgu [2I,H], Wdn [H,I]); qcfgs[e] = (q_gu, q_dn);
+    shared = (Wgu, Wdn, q_gu, q_dn) or None.  Returns fp16 [T,H]."""
+    offs, src, slot = permute(topk_ids, E)
+    xs = x[src]
+    Hd = x.shape[1]
+    down = np.zeros((len(src), Hd), f16)
+    for e in range(E):
+        r = slice(offs[e], offs[e + 1])
+        if offs[e] == offs[e + 1]:
+            continue
+        down[r] = expert_mlp(xs[r], weights[e][0], weights[e][1], qcfgs[e][0], qcfgs[e][1], hadamard_down)
+    sh = None
+    if shared is not None:
+        sh = expert_mlp(x, shared[0], shared[1], shared[2], shared[3], hadamard_down)
+    return combine(down, slot, topk_w, sh)

@@ -1,0 +1,75 @@
+"""End-to-end parity of the MoE-layer hot path (MoELayer.forward, all five pieces through the C-ABI) against the
+CPU oracle on a scaled-down Qwen1.5-MoE-like layer with a mixed w4a4/w8a8/fp16/w4a16 assignment."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def lin(w, a, g=-1, sym=True):
+    return {"w_bits": w, "w_gsize": g, "w_sym": sym, "w_clip": [1.0, 1.0], "a_bits": a, "a_gsize": g, "a_sym": True,
+            "a_clip": [1.0, 1.0]}
+
+
+def run_case(E, k, Hd, I, ns, T, cfgs, hadamard, seed):
+    from mxmoe_b200 import ops
+    from mxmoe_b200.config import qmodel_cfg_from_dict
+    from mxmoe_b200.layer import MoELayer
+    rng = np.random.default_rng(seed)
+    units = E + (1 if ns else 0)
+    ex = {}
+    for e in range(units):
+        gu, dn = cfgs[e % len(cfgs)]
+        ex[str(e)] = {"gate": gu, "up": dict(gu), "down": dn}
+    ql = qmodel_cfg_from_dict({"0": {"experts": ex}}).layers["0"]
+    weights = {}
+    for e in range(units):
+        Ie = I * ns if e == E else I
+        # 1/sqrt(K)-scaled weights keep the fp16 activations in range through two GEMMs
+        weights[e] = (((rng.random((2 * Ie, Hd)) * 2 - 1) * (2.0 / np.sqrt(Hd))).astype(np.float16),
+                      ((rng.random((Hd, Ie)) * 2 - 1) * (2.0 / np.sqrt(Ie))).astype(np.float16))
+    x = (rng.random((T, Hd)) * 2 - 1).astype(np.float16)
+    ids = np.stack([rng.permutation(E)[:k] for _ in range(T)]).astype(np.int32)
+    w = rng.random((T, k)).astype(np.float32)
+    w /= w.sum(1, keepdims=True)
+    h = ops.Handle(0)
+    layer = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, hadamard_down=hadamard,
+                     weights={e: (torch.from_numpy(a), torch.from_numpy(b)) for e, (a, b) in weights.items()})
+    out = layer.forward(torch.from_numpy(x).cuda(), torch.from_numpy(ids).cuda(), torch.from_numpy(w).cuda())
+    out2 = layer.forward(torch.from_numpy(x).cuda(), torch.from_numpy(ids).cuda(), torch.from_numpy(w).cuda())
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2), "the layer is not deterministic"
+
+    def q(c):
+        return (c["w_bits"], c["a_bits"], c["w_gsize"], c["w_sym"])
+    qc = [(q(ex[str(e)]["gate"]), q(ex[str(e)]["down"])) for e in range(units)]
+    shared = (weights[E][0], weights[E][1], qc[E][0], qc[E][1]) if ns else None
+    ref = O.moe_layer(x, ids, w, weights, qc, E, hadamard, shared)
+    return out.cpu().numpy(), ref
+
+
+def test_layer_integer_paths_bit_exact():
+    """w8a8 / w4a4 only, no Hadamard: every stage is integer/fp16-exact, so the whole layer is bit-exact
+    except where silu's expf differs from numpy's exp by an fp16 rounding (tolerated: <0.5% of outputs, 1e-3 rel)."""
+    cfgs = [(lin(8, 8), lin(4, 4)), (lin(4, 4), lin(4, 4)), (lin(4, 4), lin(8, 8))]
+    out, ref = run_case(E=6, k=2, Hd=256, I=128, ns=2, T=96, cfgs=cfgs, hadamard=False, seed=0)
+    o, r = out.astype(np.float64), ref.astype(np.float64)
+    assert np.mean(o != r) < 5e-3
+    assert np.abs(o - r).max() <= 1e-2 * np.abs(r).max()
+
+
+def test_layer_mixed_with_hadamard():
+    """Mixed fp16 / w4a16_g128_asym / w8a8 / w4a4 with the online Hadamard on the down input (I = 176 * 8 = 1408).
+    Tolerance: north_star's 1e-3 max relative error applies per GEMM on identical inputs; through
+    quantize->GEMM->silu->Hadamard->quantize->GEMM a one-step code flip moves an output by one quantization
+    step, so the end-to-end bar is 2e-2 of the output range with 99% of the elements within 2e-3."""
+    cfgs = [(lin(16, 16), lin(16, 16)), (lin(4, 16, 128, False), lin(4, 16, 128, False)), (lin(8, 8), lin(4, 4)),
+            (lin(4, 4), lin(8, 8))]
+    out, ref = run_case(E=4, k=2, Hd=256, I=1408, ns=0, T=64, cfgs=cfgs, hadamard=True, seed=1)
+    o, r = out.astype(np.float64), ref.astype(np.float64)
+    scale = np.abs(r).max()
+    assert np.abs(o - r).max() <= 2e-2 * scale
+    assert np.mean(np.abs(o - r) > 2e-3 * scale) < 0.01
