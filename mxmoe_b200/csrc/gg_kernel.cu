@@ -34,6 +34,7 @@ struct SmemLayout {
   uint64_t* full;        // [GG_STAGES] TMA landed
   uint64_t* empty;       // [GG_STAGES] MMA finished reading
   uint64_t* conv;        // [GG_STAGES] converters finished writing B
+  uint64_t* cfull;       // [GG_STAGES] packed B landed (used ONLY by converted tiles, so converter warps see every phase)
   uint64_t* tmem_full;   // [2]
   uint64_t* tmem_empty;  // [2]
   uint32_t* tmem_ptr;
@@ -52,7 +53,8 @@ __device__ __forceinline__ SmemLayout carve(uint8_t* raw) {
   s.full = reinterpret_cast<uint64_t*>(p);
   s.empty = s.full + GG_STAGES;
   s.conv = s.empty + GG_STAGES;
-  s.tmem_full = s.conv + GG_STAGES;
+  s.cfull = s.conv + GG_STAGES;
+  s.tmem_full = s.cfull + GG_STAGES;
   s.tmem_empty = s.tmem_full + 2;
   s.tmem_ptr = reinterpret_cast<uint32_t*>(s.tmem_empty + 2);
   s.prefix = reinterpret_cast<int32_t*>(p + 256);
@@ -133,6 +135,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
       mbar_init(&S.full[i], 1);
       mbar_init(&S.empty[i], 1);
       mbar_init(&S.conv[i], 4);
+      mbar_init(&S.cfull[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&S.tmem_full[i], 1);
@@ -178,13 +181,22 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
         const int b_row = n_blk * d.bn;
         const int kblocks = d.kblocks, a_kstep = d.a_kstep, b_kstep = d.b_kstep;
         const uint32_t tx = d.tx_bytes;
-        const int b_off = d.conv != CONV_NONE ? GG_PACKED_OFF : 0;
+        const bool has_conv = d.conv != CONV_NONE;
+        const int b_off = has_conv ? GG_PACKED_OFF : 0;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&S.empty[stage], phase ^ 1);
           uint8_t* sa = S.stages + stage * GG_STAGE_BYTES;
-          mbar_expect_tx(&S.full[stage], tx);
+          // converted tiles: A lands on `full`, the packed B on `cfull` (a barrier whose every phase the
+          // converter warps observe; waiting on `full` from a role that skips tiles would alias phases)
+          uint64_t* bbar = has_conv ? &S.cfull[stage] : &S.full[stage];
+          if (has_conv) {
+            mbar_expect_tx(&S.full[stage], GG_A_BYTES);
+            mbar_expect_tx(bbar, tx - GG_A_BYTES);
+          } else {
+            mbar_expect_tx(&S.full[stage], tx);
+          }
           tma_load_2d(sa, &d.tmA, &S.full[stage], kb * a_kstep, a_row);
-          tma_load_2d(sa + GG_A_BYTES + b_off, &d.tmB, &S.full[stage], kb * b_kstep, b_row);
+          tma_load_2d(sa + GG_A_BYTES + b_off, &d.tmB, bbar, kb * b_kstep, b_row);
           if (++stage == GG_STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -363,15 +375,13 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
     // ============================================================ operand converters (4 warps)
     const int ct = threadIdx.x - 256;  // 0..127
     int stage = 0;
-    uint32_t phase = 0;
+    uint32_t cphase_bits = 0;  // per-stage parity of `cfull` (advances only on converted tiles)
     for (TileWalk w(S.prefix, P); w.valid(); w.advance()) {
       const DevProblem& d = probs[w.p];
       const int kblocks = d.kblocks;
       const int conv = d.conv;
       if (conv == CONV_NONE) {  // nothing to do: just keep the ring position in step
-        int adv = stage + kblocks;
-        phase ^= (adv / GG_STAGES) & 1;
-        stage = adv % GG_STAGES;
+        stage = (stage + kblocks) % GG_STAGES;
         continue;
       }
       const int bn = d.bn;
@@ -380,7 +390,8 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
       const int n0 = n_blk * bn;
       if (conv == CONV_W4_I8) {
         for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&S.full[stage], phase);
+          mbar_wait(&S.cfull[stage], (cphase_bits >> stage) & 1);
+          cphase_bits ^= 1u << stage;
           uint8_t* bfin = S.stages + stage * GG_STAGE_BYTES + GG_A_BYTES;
           const uint8_t* bpk = bfin + GG_PACKED_OFF;
           // packed tile: bn rows x 64 B (128 k as nibbles); 16-byte item = 32 k: low nibbles k..k+15, high k+16..k+31
@@ -399,7 +410,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(&S.conv[stage]);
-          if (++stage == GG_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == GG_STAGES) stage = 0;
         }
       } else {
         // W-only: unsigned codes -> fp16 via the 0x6400 magic, then w = hfma(q, scale, zp) (quantize.cuh:189-190)
@@ -432,7 +443,8 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
               }
             }
           }
-          mbar_wait(&S.full[stage], phase);
+          mbar_wait(&S.cfull[stage], (cphase_bits >> stage) & 1);
+          cphase_bits ^= 1u << stage;
           uint8_t* bfin = S.stages + stage * GG_STAGE_BYTES + GG_A_BYTES;
           const uint8_t* bpk = bfin + GG_PACKED_OFF;
 #pragma unroll
@@ -485,7 +497,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(&S.conv[stage]);
-          if (++stage == GG_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == GG_STAGES) stage = 0;
         }
       }
     }

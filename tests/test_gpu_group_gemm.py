@@ -199,3 +199,53 @@ def test_full_size_int8_property(H):
                      acc_out=[acc])
         torch.cuda.synchronize()
         assert torch.equal(acc, ref), f"w{w_bits}: int32 accumulators differ at full size"
+
+
+def test_many_tiles_per_cta_mixed_kinds(H):
+    """Regression: every CTA walks MANY tiles whose kinds alternate (converted w4a4 / plain w8a8 / fp16 / w4a16),
+    so the smem ring, the converter barriers and the two TMEM accumulators all wrap several times.
+    Checked against exact float64 matmuls on the device (int32 accumulators bit-exact; fp16 within 1e-3)."""
+    from mxmoe_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(7)
+    rng = np.random.default_rng(7)
+    K = 512
+    probs, checks, accs = [], [], []
+    for i in range(12):
+        kind = i % 4
+        M, N = 700 + 37 * i, 1024
+        Cb = torch.full((M, N), float("nan"), dtype=torch.float16, device="cuda")
+        if kind in (0, 1):
+            bits = 4 if kind == 0 else 8
+            hi = (1 << (bits - 1)) - 1
+            qa = torch.randint(-hi, hi + 1, (M, K), generator=g, device="cuda", dtype=torch.int32)
+            qw = torch.randint(-hi, hi + 1, (N, K), generator=g, device="cuda", dtype=torch.int32)
+            B = qw.to(torch.int8) if bits == 8 else dev(O.pack_wxax_native(qw.cpu().numpy(), 4))
+            acc = torch.zeros(M, N, dtype=torch.int32, device="cuda")
+            probs.append(ops.Problem(qa.to(torch.int8), B, Cb, M, N, K, bits, bits, -1, True,
+                                     scale_a=torch.ones(M, dtype=torch.float16, device="cuda"),
+                                     scale_b=torch.ones(N, dtype=torch.float16, device="cuda")))
+            accs.append(acc)
+            checks.append(("int", (qa.double() @ qw.double().T).to(torch.int32), acc))
+        elif kind == 2:
+            A = (torch.rand(M, K, generator=g, device="cuda") * 2 - 1).half()
+            Wt = (torch.rand(N, K, generator=g, device="cuda") * 2 - 1).half()
+            probs.append(ops.Problem(A, Wt, Cb, M, N, K))
+            accs.append(None)
+            checks.append(("f16", A.double() @ Wt.double().T, Cb))
+        else:
+            A = (torch.rand(M, K, generator=g, device="cuda") * 2 - 1).half()
+            Wn = rand16(rng, N, K)
+            q, s, z = O.quant_weight(Wn, 4, 128, False)
+            probs.append(ops.Problem(A, dev(O.pack_weightonly_native(q, 4, False)), Cb, M, N, K, 4, 16, 128, False,
+                                     scale_b=dev(O.permute_scale(s, z, False))))
+            accs.append(None)
+            Wd = torch.from_numpy(O.dequant_wonly(q, s, z, 128, False)).cuda()
+            checks.append(("f16", A.double() @ Wd.double().T, Cb))
+    H.group_gemm(probs, acc_out=accs)
+    torch.cuda.synchronize()
+    for i, (kind, ref, got) in enumerate(checks):
+        if kind == "int":
+            assert torch.equal(got, ref), f"problem {i}: int32 accumulators differ"
+        else:
+            err = (got.double() - ref).abs().max().item() / ref.abs().max().item()
+            assert err <= REL_TOL, f"problem {i}: rel err {err}"
