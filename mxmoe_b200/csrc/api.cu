@@ -138,7 +138,7 @@ int classify(const MxbProblem& p, KindInfo* k) {
 
 int pick_tile_n(const MxbProblem& p, const KindInfo& k) {
   int cap = 256;
-  if (k.conv != mxb::CONV_NONE) cap = 128;
+  if (k.conv >= mxb::CONV_W4_F16) cap = 128;  // weight-only converters own 2 rows per thread
   if (k.epi == mxb::EPI_INT_GROUP) cap = 64;
   int bn = p.tile_n > 0 ? p.tile_n : cap;
   if (bn > cap) bn = cap;
@@ -499,7 +499,7 @@ int quant_common(mxb_context* c, bool silu, const void* x, int H, const int32_t*
       if (rc) return rc;
     }
     cudaError_t e = mxb::hadamard_quant_launch(silu, x, H, src_row, n_rows, expert_offsets, tab, E, out_q8, out_f16, scales,
-                                               scale_cols, hmat, K, Kp, c->sm_count, st);
+                                               scale_cols, hmat, K, Kp, c->sm_count, g128 != 0, st);
     if (e != cudaSuccess) return fail(MXB_ECUDA, "hadamard_quant_launch: %s", cudaGetErrorString(e));
     return MXB_OK;
   }

@@ -394,18 +394,27 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
           cphase_bits ^= 1u << stage;
           uint8_t* bfin = S.stages + stage * GG_STAGE_BYTES + GG_A_BYTES;
           const uint8_t* bpk = bfin + GG_PACKED_OFF;
-          // packed tile: bn rows x 64 B (128 k as nibbles); 16-byte item = 32 k: low nibbles k..k+15, high k+16..k+31
-          for (int i = ct; i < bn * 4; i += 128) {
-            const int row = i >> 2, c = i & 3;
-            uint4 w4 = *reinterpret_cast<const uint4*>(bpk + row * 64 + c * 16);
-            uint4 lo, hi;
-            lo.x = (w4.x << 4) & 0xF0F0F0F0u; hi.x = w4.x & 0xF0F0F0F0u;
-            lo.y = (w4.y << 4) & 0xF0F0F0F0u; hi.y = w4.y & 0xF0F0F0F0u;
-            lo.z = (w4.z << 4) & 0xF0F0F0F0u; hi.z = w4.z & 0xF0F0F0F0u;
-            lo.w = (w4.w << 4) & 0xF0F0F0F0u; hi.w = w4.w & 0xF0F0F0F0u;
-            const int sw = row & 7;
-            *reinterpret_cast<uint4*>(bfin + row * 128 + (((2 * c) ^ sw) << 4)) = lo;
-            *reinterpret_cast<uint4*>(bfin + row * 128 + (((2 * c + 1) ^ sw) << 4)) = hi;
+          // packed tile: bn rows x 64 B (128 k as nibbles); 16-byte item = 32 k: low nibbles k..k+15, high k+16..k+31.
+          // bn/32 items per thread; all loads are issued before the first store (ILP against the smem latency).
+          const int iters = bn >> 5;
+          uint4 w4[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (j < iters) w4[j] = *reinterpret_cast<const uint4*>(bpk + (ct + j * 128) * 16);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (j < iters) {
+              const int i = ct + j * 128;
+              const int row = i >> 2, c = i & 3;
+              uint4 lo, hi;
+              lo.x = (w4[j].x << 4) & 0xF0F0F0F0u; hi.x = w4[j].x & 0xF0F0F0F0u;
+              lo.y = (w4[j].y << 4) & 0xF0F0F0F0u; hi.y = w4[j].y & 0xF0F0F0F0u;
+              lo.z = (w4[j].z << 4) & 0xF0F0F0F0u; hi.z = w4[j].z & 0xF0F0F0F0u;
+              lo.w = (w4[j].w << 4) & 0xF0F0F0F0u; hi.w = w4[j].w & 0xF0F0F0F0u;
+              const int sw = row & 7;
+              *reinterpret_cast<uint4*>(bfin + row * 128 + (((2 * c) ^ sw) << 4)) = lo;
+              *reinterpret_cast<uint4*>(bfin + row * 128 + (((2 * c + 1) ^ sw) << 4)) = hi;
+            }
           }
           fence_proxy_async_smem();
           __syncwarp();

@@ -37,7 +37,7 @@ struct alignas(128) DevProblem {
   int32_t M, N, K;
   int32_t mma_kind, conv, epi;
   int32_t acc_shift;
-  int32_t bn;       // tile N (UMMA N), multiple of 16, <= 256 (<= 128 when conv != NONE)
+  int32_t bn;       // tile N (UMMA N): 32/64/128/256 (<= 128 for the weight-only converters)
   int32_t n_tiles;  // ceil(N / bn)
   int32_t kblocks;  // number of 128-byte K slabs of the MMA operand
   int32_t a_kstep;  // tensor-map coordinate step per k-block (elements of the map's dtype)
@@ -53,11 +53,12 @@ static_assert(sizeof(DevProblem) == 384, "DevProblem layout");
 constexpr int GG_MAXP = 256;       // problems per launch (host splits longer lists)
 constexpr int GG_THREADS = 384;    // 12 warps: TMA, MMA, TMEM-alloc, spare, 4 epilogue, 4 converter
 constexpr int GG_BM = 128;
-constexpr int GG_STAGES = 4;
+constexpr int GG_STAGES = 3;
 constexpr int GG_A_BYTES = 128 * 128;   // 128 rows x 128 B
 constexpr int GG_B_BYTES = 256 * 128;   // up to 256 rows x 128 B
-constexpr int GG_STAGE_BYTES = GG_A_BYTES + GG_B_BYTES;
-constexpr int GG_PACKED_OFF = 128 * 128;  // packed staging inside the B region when conv != NONE
+constexpr int GG_PACKED_BYTES = 256 * 64;  // raw 4/8-bit weight slab staged for the converter warps
+constexpr int GG_STAGE_BYTES = GG_A_BYTES + GG_B_BYTES + GG_PACKED_BYTES;
+constexpr int GG_PACKED_OFF = GG_B_BYTES;  // offset of the packed staging from the start of the B region
 constexpr int GG_EPI_STAGE_BYTES = 4 * 32 * 64;
 constexpr int GG_SMEM_BYTES = 1024 /*align slack*/ + GG_STAGES * GG_STAGE_BYTES + GG_EPI_STAGE_BYTES + 256 /*barriers*/ +
                               (3 * GG_MAXP + 4) * 4;

@@ -18,7 +18,7 @@ int hadamard_factor(int n);
 cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t* src_row, int n_rows,
                                   const int32_t* expert_offsets, const int32_t* actq_dev, int E, void* out_q8, void* out_f16,
                                   void* scales, int scale_cols, const void* hmat_dev, int K, int Kp, int sm_count,
-                                  cudaStream_t st);
+                                  bool any_g128, cudaStream_t st);
 
 cudaError_t combine_launch(const void* down, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
                            const void* shared_out, void* out, cudaStream_t st);
