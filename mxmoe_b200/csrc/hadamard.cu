@@ -37,6 +37,13 @@ __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4],
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
 }
 
+__device__ __forceinline__ uint4 ptx_ld_nc(const __half* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
 struct HadParams {
   const __half* x;
   int n;              // row length after silu*mul (I) or H
@@ -191,193 +198,7 @@ __global__ void __launch_bounds__(256) hadamard_quant_kernel(HadParams p) {
 }
 
 
-// ---------------------------------------------------------------------------------------------------------
-// Fast path (K > 1, 8 <= m <= 128, per-token or fp16 output): a CTA rotates BATCHES of rows on the tensor
-// cores.  For a batch of R = 128/m rows the K-axis product is one GEMM  Y[K, 128] = hadK[K, K] @ X[K, 128]
-// whose B operand is the batch itself laid out [j][row*m + c] in shared memory.  Every warp keeps its A
-// fragments (its 16-row slices of hadK) in registers for the whole kernel, so per batch a warp only issues
-// ldmatrix.trans for B and mma.sync.  The fp16-rounded result goes back to shared memory, the per-row absmax
-// is collected with shared atomics, and the quantized row is written to HBM in one coalesced pass.
-template <int KT, bool SILU>
-__global__ void __launch_bounds__(256, 2) hadamard_mma_kernel(HadParams p) {
-  extern __shared__ __align__(16) uint8_t hsm[];
-  constexpr int NCOLS = 128;
-  constexpr int PITCH = NCOLS * 2 + 16;  // bytes per k-row of the staged batch (+16: conflict-free ldmatrix)
-  constexpr int KP = KT * 16;
-  uint8_t* Xs = hsm;
-  uint8_t* Ys = hsm + KP * PITCH;
-  __shared__ unsigned int tokmax[16];
-  __shared__ int tok_bits[16];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n = p.n, n8 = n >> 3, m = p.m, R = NCOLS / m;
-
-  // ---- A fragments: stage hadK once through shared memory, keep this warp's slices in registers
-  for (int i = threadIdx.x; i < KP * (KP / 8); i += 256) {
-    const int r = i / (KP / 8), c = i % (KP / 8);
-    *reinterpret_cast<uint4*>(hsm + r * p.h_pitch + c * 16) = *reinterpret_cast<const uint4*>(p.hmat + r * KP + c * 8);
-  }
-  __syncthreads();
-  uint32_t af[2][KT][4];
-#pragma unroll
-  for (int s = 0; s < 2; ++s) {
-    const int mt = warp + 8 * s;
-#pragma unroll
-    for (int kt = 0; kt < KT; ++kt) {
-      if (mt < KT) ldsm_x4(s_u32(hsm) + (mt * 16 + (lane & 15)) * p.h_pitch + (kt * 16 + (lane >> 4) * 8) * 2, af[s][kt]);
-      else af[s][kt][0] = af[s][kt][1] = af[s][kt][2] = af[s][kt][3] = 0u;
-    }
-  }
-  __syncthreads();
-  // rows K..KP-1 of the B operand stay zero for the whole kernel
-  for (int i = threadIdx.x; i < (KP - p.K) * (PITCH / 16); i += 256)
-    *reinterpret_cast<uint4*>(Xs + p.K * PITCH + i * 16) = make_uint4(0, 0, 0, 0);
-
-  const int n_batches = (p.n_rows + R - 1) / R;
-  for (int b = blockIdx.x; b < n_batches; b += gridDim.x) {
-    const int row0 = b * R;
-    if (threadIdx.x < 16) {
-      tokmax[threadIdx.x] = 0u;
-      int bits = 0;  // 0 = row not owned (past the end): skip
-      const int row = row0 + threadIdx.x;
-      if (threadIdx.x < R && row < p.n_rows) {
-        bits = p.actq[0].x;
-        if (p.E > 1) {
-          if (row >= p.expert_offsets[p.E]) bits = 0;
-          else bits = p.actq[find_expert(p.expert_offsets, p.E, row)].x;
-        }
-      }
-      tok_bits[threadIdx.x] = bits;
-    }
-    // ---- load (+silu*mul), FWHT over m (registers + shuffles), scale, stage as fp16 [j][r*m + c]
-    const int chunks = R * n8;
-    for (int q0 = 0; q0 < chunks; q0 += 256) {
-      const int q = q0 + threadIdx.x;
-      const int r = q / n8, idx8 = q - r * n8;
-      const int row = row0 + r;
-      float v[8];
-      const bool live = q < chunks && row < p.n_rows;
-      if (live) {
-        const int64_t srow = p.src_row ? p.src_row[row] : row;
-        load8<SILU>(p.x + srow * p.in_pitch, n, idx8, v);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = 0.f;
-      }
-#pragma unroll
-      for (int h = 1; h < 8; h <<= 1) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if ((j & h) == 0) {
-            const float a = v[j], bb = v[j + h];
-            v[j] = a + bb;
-            v[j + h] = a - bb;
-          }
-        }
-      }
-      // strides 8 .. m/2 live in neighbouring lanes (n8 and 256 are multiples of m/8, so groups never straddle a warp)
-      for (int h = 8; h < m; h <<= 1) {
-        const int lm = h >> 3;
-        const bool upper = (lane & lm) != 0;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float o = __shfl_xor_sync(0xffffffffu, v[j], lm);
-          v[j] = upper ? o - v[j] : v[j] + o;
-        }
-      }
-      if (q < chunks) {
-        uint4 pk;
-        __half2* ph = reinterpret_cast<__half2*>(&pk);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) ph[j] = __floats2half2_rn(v[2 * j] * p.scale, v[2 * j + 1] * p.scale);
-        const int e = idx8 * 8, j = e / m, c0 = e - j * m;
-        *reinterpret_cast<uint4*>(Xs + j * PITCH + (r * m + c0) * 2) = pk;
-      }
-    }
-    __syncthreads();
-    // ---- Y = hadK @ X on the tensor cores
-    {
-      float tmax = 0.f;
-      int cur_tok = 0;
-      const uint32_t xs = s_u32(Xs);
-#pragma unroll 1
-      for (int nt = 0; nt < NCOLS / 8; ++nt) {
-        const int tok = (nt * 8) / m;
-        if (tok != cur_tok) {
-          tmax = warp_max(tmax);
-          if (lane == 0) atomicMax(&tokmax[cur_tok], __float_as_uint(tmax));
-          tmax = 0.f;
-          cur_tok = tok;
-        }
-        uint32_t bf[KT][2];
-#pragma unroll
-        for (int kt = 0; kt < KT; ++kt) ldsm_x2_trans(xs + (kt * 16 + (lane & 15)) * PITCH + nt * 16, bf[kt]);
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          const int mt = warp + 8 * s;
-          if (mt < KT) {
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-            for (int kt = 0; kt < KT; ++kt) mma_16816(acc, af[s][kt], bf[kt]);
-            const __half2 h01 = __floats2half2_rn(acc[0], acc[1]), h23 = __floats2half2_rn(acc[2], acc[3]);
-            const int r0 = mt * 16 + (lane >> 2), cb = (nt * 8 + (lane & 3) * 2) * 2;
-            *reinterpret_cast<__half2*>(Ys + r0 * PITCH + cb) = h01;
-            *reinterpret_cast<__half2*>(Ys + (r0 + 8) * PITCH + cb) = h23;
-            const float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
-            tmax = fmaxf(tmax, fmaxf(fmaxf(fabsf(f01.x), fabsf(f01.y)), fmaxf(fabsf(f23.x), fabsf(f23.y))));
-          }
-        }
-      }
-      tmax = warp_max(tmax);
-      if (lane == 0) atomicMax(&tokmax[cur_tok], __float_as_uint(tmax));
-    }
-    __syncthreads();
-    // ---- quantize straight from shared memory, coalesced row-major stores
-    for (int q = threadIdx.x; q < chunks; q += 256) {
-      const int r = q / n8, idx8 = q - r * n8;
-      const int bits = tok_bits[r];
-      if (bits == 0) continue;
-      const int row = row0 + r;
-      const int e = idx8 * 8, j = e / m, c0 = e - j * m;
-      const uint4 u = *reinterpret_cast<const uint4*>(Ys + j * PITCH + (r * m + c0) * 2);
-      if (bits >= 16) {
-        *reinterpret_cast<uint4*>(p.out_f16 + static_cast<int64_t>(row) * n + e) = u;
-      } else {
-        const float upper = static_cast<float>((1 << (bits - 1)) - 1);
-        const __half sh = make_scale(__uint_as_float(tokmax[r]), upper);
-        if (idx8 == 0) p.scales[static_cast<int64_t>(row) * p.scale_cols] = sh;
-        const __half* uh = reinterpret_cast<const __half*>(&u);
-        float v[8];
-#pragma unroll
-        for (int jj = 0; jj < 8; ++jj) v[jj] = __half2float(uh[jj]);
-        *reinterpret_cast<uint2*>(p.out_q8 + static_cast<int64_t>(row) * n + e) = quant8(v, __half2float(sh), upper);
-      }
-    }
-    __syncthreads();
-  }
-}
-
-template <int KT>
-cudaError_t launch_mma(bool silu, const HadParams& p, int sm_count, cudaStream_t st) {
-  constexpr int PITCH = 128 * 2 + 16;
-  const int KP = KT * 16;
-  int smem = 2 * KP * PITCH;
-  if (smem < KP * p.h_pitch) smem = KP * p.h_pitch;
-  const int R = 128 / p.m;
-  const int n_batches = (p.n_rows + R - 1) / R;
-  int grid = sm_count * 2;
-  if (grid > n_batches) grid = n_batches;
-  cudaError_t e;
-  if (silu) {
-    e = cudaFuncSetAttribute(hadamard_mma_kernel<KT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    hadamard_mma_kernel<KT, true><<<grid, 256, smem, st>>>(p);
-  } else {
-    e = cudaFuncSetAttribute(hadamard_mma_kernel<KT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    hadamard_mma_kernel<KT, false><<<grid, 256, smem, st>>>(p);
-  }
-  return cudaGetLastError();
-}
+#include "hadamard_mma.inc"
 
 }  // namespace
 

@@ -21,10 +21,12 @@ __device__ __forceinline__ float half_warp_max(float v) {  // reduce inside each
 }
 __device__ __forceinline__ float h_round(float x) { return __half2float(__float2half_rn(x)); }
 
-// act_fn(gate) * up on fp16 tensors: silu evaluated in fp32 and rounded to fp16, product rounded to fp16
+// act_fn(gate) * up on fp16 tensors: silu evaluated in fp32 and rounded to fp16, product rounded to fp16.
+// ex2.approx / rcp.approx (a few fp32 ulp) instead of expf + IEEE division: after the fp16 rounding the result
+// equals the exactly-rounded one except in ~5e-4 of the elements (one fp16 ulp) — the kernel is issue-bound.
 __device__ __forceinline__ float silu_mul_h(__half g, __half u) {
-  float gf = __half2float(g);
-  float s = h_round(__fdiv_rn(gf, 1.f + expf(-gf)));
+  const float gf = __half2float(g);
+  const float s = h_round(__fdividef(gf, 1.f + __expf(-gf)));
   return h_round(s * __half2float(u));
 }
 
@@ -54,14 +56,21 @@ __device__ __forceinline__ int find_expert(const int32_t* __restrict__ offs, int
   return lo;
 }
 
-__device__ __forceinline__ uint2 quant8(const float (&v)[8], float sf, float upper) {
+// q = rint(clamp(half(x / s))) with torch's fp16 semantics (fp32 divide, round to fp16).  The IEEE division is
+// replaced by a per-row correctly-rounded reciprocal plus one Newton correction per element:
+//   q0 = x*r;  q1 = q0 + (x - q0*s)*r   (|q1 - x/s| <= 0.5 ulp + 2^-40)
+// x and s are fp16 values, so x/s is either exactly representable in fp32 or at least one fp32 ulp away from every
+// fp16 rounding boundary: half(q1) == half(x/s) always (and the GPU tests compare bit-for-bit with the oracle).
+__device__ __forceinline__ uint2 quant8(const float (&v)[8], float sf, float rcp, int upper) {
   uint2 pk;
   int8_t* pb = reinterpret_cast<int8_t*>(&pk);
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    float q = h_round(__fdiv_rn(v[j], sf));
-    q = rintf(fminf(fmaxf(q, -upper), upper));
-    pb[j] = static_cast<int8_t>(static_cast<int>(q));
+    const float q0 = v[j] * rcp;
+    const float q1 = fmaf(fmaf(-q0, sf, v[j]), rcp, q0);
+    int qi = __float2int_rn(h_round(q1));
+    qi = max(-upper, min(upper, qi));
+    pb[j] = static_cast<int8_t>(qi);
   }
   return pk;
 }
@@ -89,7 +98,8 @@ __device__ __forceinline__ void quantize_row(Loader ld, int H, int lane, int a_b
     }
     return;
   }
-  const float upper = static_cast<float>((1 << (a_bits - 1)) - 1);
+  const int iupper = (1 << (a_bits - 1)) - 1;
+  const float upper = static_cast<float>(iupper);
   if (gsize <= 0) {
     float amax = 0.f;
     for (int i = lane; i < n8; i += 32) {
@@ -100,12 +110,12 @@ __device__ __forceinline__ void quantize_row(Loader ld, int H, int lane, int a_b
     }
     amax = warp_max(amax);
     const __half sh = make_scale(amax, upper);
-    const float sf = __half2float(sh);
+    const float sf = __half2float(sh), rcp = __frcp_rn(sf);
     if (lane == 0) so[0] = sh;
     for (int i = lane; i < n8; i += 32) {
       float v[8];
       ld(i, v);
-      *reinterpret_cast<uint2*>(o_q8 + i * 8) = quant8(v, sf, upper);
+      *reinterpret_cast<uint2*>(o_q8 + i * 8) = quant8(v, sf, rcp, iupper);
     }
   } else {  // gsize == 128: 16 lanes x 8 elements per group
     const int iters = (n8 + 31) / 32;
@@ -125,7 +135,8 @@ __device__ __forceinline__ void quantize_row(Loader ld, int H, int lane, int a_b
       const __half sh = make_scale(amax, upper);
       if (i < n8) {
         if ((lane & 15) == 0) so[i >> 4] = sh;
-        *reinterpret_cast<uint2*>(o_q8 + i * 8) = quant8(v, __half2float(sh), upper);
+        const float sf = __half2float(sh);
+        *reinterpret_cast<uint2*>(o_q8 + i * 8) = quant8(v, sf, __frcp_rn(sf), iupper);
       }
     }
   }

@@ -82,17 +82,18 @@ def test_silu_mul_quant(H):
     torch.cuda.synchronize()
     q8, f16, sc = q8.cpu().numpy(), f16.cpu().numpy(), sc.cpu().numpy()
     h = O.silu_mul(gu)
-    # expf on the device vs numpy exp: identical after the fp16 rounding except at rounding boundaries
+    # ex2.approx+rcp.approx on the device vs numpy exp: identical after the fp16 rounding except at rounding
+    # boundaries (expected ~5e-4 of the elements, one fp16 ulp)
     got = f16[120:200].astype(np.float32)
     ref = h[120:200].astype(np.float32)
-    assert np.mean(got != ref) < 2e-3 and np.abs(got - ref).max() <= 2 ** -8 * np.abs(ref).max()
+    assert np.mean(got != ref) < 5e-3 and np.abs(got - ref).max() <= 2 ** -8 * np.abs(ref).max()
     for e, (a, g) in enumerate(actq[:3]):
         r = slice(offs[e], offs[e + 1])
         if offs[e] == offs[e + 1]:
             continue
         rq, rs = O.quant_act(h[r], a, g)
         # tolerance: a 1-ulp difference in h can move a code by one step and, if it is the row maximum, the scale by 1 ulp
-        assert np.mean(q8[r].astype(np.int32) != rq) < 5e-3
+        assert np.mean(q8[r].astype(np.int32) != rq) < 1e-2
         assert np.abs(q8[r].astype(np.int32) - rq).max() <= 1
         assert np.abs(sc[r, 0].astype(np.float32) - rs[:, 0].astype(np.float32)).max() <= 2 ** -10 * np.abs(rs.astype(np.float32)).max()
 
