@@ -109,3 +109,31 @@ def test_permute_and_combine_roundtrip():
     out = O.combine(x[src], slot, w)
     np.testing.assert_allclose(out.astype(np.float32), x.astype(np.float32), atol=2e-3)
     assert flat[np.argsort(flat, kind="stable")][slot.reshape(-1)].tolist() == flat.tolist()
+
+
+def _ref_pack(op, N, K, M, qbits, sym, gsize, payload: bytes) -> bytes:
+    import subprocess
+    exe = os.path.join(os.path.dirname(__file__), "..", "oracle", "_ref", "ref_pack")
+    hdr = np.array([op, N, K, M, qbits, int(sym), gsize], np.int32).tobytes()
+    return subprocess.run([exe], input=hdr + payload, stdout=subprocess.PIPE, check=True).stdout
+
+
+@pytest.mark.parametrize("bits,sym", [(4, True), (4, False), (8, True), (2, False)])
+def test_packers_against_live_reference_binary(bits, sym):
+    """When oracle/_ref/ref_pack (the reference's own packers compiled in place by oracle/Makefile) is present,
+    check the restatement on fresh random data as well, not only on the committed goldens."""
+    exe = os.path.join(os.path.dirname(__file__), "..", "oracle", "_ref", "ref_pack")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_pack not built (no reference tree on this box)")
+    rng = np.random.default_rng(bits * 2 + sym)
+    N, K = 64, 96 if bits != 2 else 64
+    hi = (1 << (bits - 1)) - 1
+    q = (rng.integers(-hi, hi + 1, (N, K)) if sym else rng.integers(0, 1 << bits, (N, K))).astype(np.int32)
+    out = np.frombuffer(_ref_pack(0, N, K, 0, bits, sym, -1, q.tobytes()), np.uint16)
+    assert np.array_equal(O.pack_weightonly_ref(q, bits, sym).reshape(-1), out)
+    if bits in (4, 8) and sym:
+        a = rng.integers(-hi, hi + 1, (16, K)).astype(np.int32)
+        o = np.frombuffer(_ref_pack(1, N, K, 16, bits, True, -1, a.tobytes() + q.tobytes()), np.uint16)
+        pack = 16 // bits
+        assert np.array_equal(O.pack_wxax(a, bits).reshape(-1), o[:16 * K // pack])
+        assert np.array_equal(O.pack_wxax(q, bits).reshape(-1), o[16 * K // pack:])
