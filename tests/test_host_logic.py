@@ -68,3 +68,18 @@ def test_synthetic_traces_and_mixed_qconfig():
             w8 += wt * sc * (e[blk]["w_bits"] == 8)
     assert abs(4 + 4 * w8 / tot - 5.0) < 0.1
     C.qmodel_cfg_from_dict(q)
+
+
+def test_run_mxmoe_gg_cli_dry_run(tmp_path):
+    """Same CLI as the reference driver (run_mxmoe_gg.py:34-41); --dry-run writes only the workload JSON."""
+    import subprocess
+    import sys
+    root = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+    r = subprocess.run([sys.executable, os.path.join(root, "run_mxmoe_gg.py"), "--model", "qwen2_moe", "--dataset", "wiki2",
+                        "--bs", "8192", "--layer", "11", "--qconfig", os.path.join(G, "qconfig_mixed.json"), "--dry-run"],
+                       capture_output=True, text=True, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stderr
+    assert "w4a4_g-1_sym" in r.stdout and "w8a8_g-1_sym" in r.stdout
+    wl = json.load(open(os.path.join(root, "out", "workloads", "qwen2_moe-wiki2-8192-qcfg.json")))
+    assert wl["num_tokens"] == 8192 and len(wl["layer-11"]["gate_up"]) == 61
+    assert {p["w_bits"] for p in wl["layer-11"]["down"]} == {4, 8}
