@@ -55,6 +55,8 @@ struct Plan {
   uint64_t key = 0;
   int P = 0;
   mxb::DevProblem* dev = nullptr;  // device array, capacity GG_MAXP per chunk list
+  int32_t* task_prefix = nullptr;  // [P+1] slab prefix of the problems routed to the streaming kernel
+  int stream_tasks = 0, tc_problems = 0, stream_classes = 0;
   size_t cap = 0;
   uint64_t last_use = 0;
 };
@@ -192,6 +194,14 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, mxb
   d->gsize = p.gsize;
   d->sym = p.sym;
   d->scale_a_ld = (k.epi == mxb::EPI_INT_GROUP) ? p.K / 128 : 1;
+  d->A_ptr = p.A;
+  d->B_ptr = p.B;
+  d->lda = lda;
+  // Path choice (replaces the reference's per-qconfig tile lists for the memory-bound experts,
+  // tile_config.py:330-610): 4-bit weight-only problems with at most 16 rows stream through w4a16_stream.cu.
+  // With device-resident M the row capacity of the shared buffer decides (decode batches).
+  const int m_cap = p.m_range ? (p.M <= 512 ? 16 : p.M) : p.M;
+  d->path = (k.conv == mxb::CONV_W4_F16 && m_cap <= 16 && p.K % 128 == 0 && p.tile_n == 0) ? 1 : 0;
   if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k
   else if (k.conv >= mxb::CONV_W4_F16) d->kb_per_group = p.gsize == 128 ? 2 : d->kblocks;  // fp16 slabs hold 64 k
   else d->kb_per_group = d->kblocks;
@@ -267,6 +277,15 @@ int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* 
       return fail(rc, "problem %d: %s", i, m.c_str());
     }
   }
+  std::vector<int32_t> tprefix(static_cast<size_t>(P) + 1, 0);
+  int tc_problems = 0, stream_classes = 0;
+  const int rows_per_task = mxb::w4a16_stream_rows_per_task();
+  for (int i = 0; i < P; ++i) {
+    const bool st_path = host[i].path != 0;
+    if (st_path) stream_classes |= host[i].path;
+    tprefix[i + 1] = tprefix[i] + (st_path ? (host[i].N + rows_per_task - 1) / rows_per_task : 0);
+    if (!st_path && host[i].n_tiles > 0 && !(problems[i].M == 0 && !problems[i].m_range)) ++tc_problems;
+  }
   Plan* slot = nullptr;
   if ((int)c->plans.size() < kMaxPlans) {
     c->plans.emplace_back();
@@ -279,11 +298,18 @@ int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* 
   }
   if (slot->cap < size_t(P)) {
     if (slot->dev) cudaFree(slot->dev);
+    if (slot->task_prefix) cudaFree(slot->task_prefix);
     slot->dev = nullptr;
+    slot->task_prefix = nullptr;
     slot->cap = 0;
     CU_OK(cudaMalloc(reinterpret_cast<void**>(&slot->dev), sizeof(mxb::DevProblem) * size_t(P)));
+    CU_OK(cudaMalloc(reinterpret_cast<void**>(&slot->task_prefix), sizeof(int32_t) * (size_t(P) + 1)));
     slot->cap = size_t(P);
   }
+  CU_OK(cudaMemcpyAsync(slot->task_prefix, tprefix.data(), sizeof(int32_t) * (size_t(P) + 1), cudaMemcpyHostToDevice, st));
+  slot->stream_tasks = tprefix[P];
+  slot->tc_problems = tc_problems;
+  slot->stream_classes = stream_classes;
   // pageable source: the runtime stages the bytes before returning, so `host` may die right after
   CU_OK(cudaMemcpyAsync(slot->dev, host.data(), sizeof(mxb::DevProblem) * size_t(P), cudaMemcpyHostToDevice, st));
   slot->key = key;
@@ -302,9 +328,12 @@ int group_gemm_impl(mxb_context* c, const MxbProblem* problems, int P, int32_t* 
   Plan* pl = nullptr;
   int rc = get_plan(c, problems, P, acc_out, st, &pl);
   if (rc) return rc;
-  for (int off = 0; off < P; off += mxb::GG_MAXP) {
-    const int n = P - off < mxb::GG_MAXP ? P - off : mxb::GG_MAXP;
-    mxb::gg_launch(pl->dev + off, n, c->sm_count, st);
+  if (pl->stream_tasks > 0) mxb::w4a16_stream_launch(pl->dev, P, pl->task_prefix, pl->stream_tasks, pl->stream_classes, st);
+  if (pl->tc_problems > 0) {
+    for (int off = 0; off < P; off += mxb::GG_MAXP) {
+      const int n = P - off < mxb::GG_MAXP ? P - off : mxb::GG_MAXP;
+      mxb::gg_launch(pl->dev + off, n, c->sm_count, st);
+    }
   }
   CU_OK(cudaGetLastError());
   return MXB_OK;
@@ -358,8 +387,10 @@ int mxb_destroy(mxb_handle_t c) {
   if (!c) return MXB_OK;
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
-  for (auto& pl : c->plans)
+  for (auto& pl : c->plans) {
     if (pl.dev) cudaFree(pl.dev);
+    if (pl.task_prefix) cudaFree(pl.task_prefix);
+  }
   for (auto& t : c->tables)
     if (t.dev) cudaFree(t.dev);
   for (auto* p : c->inv_tab)
@@ -654,7 +685,7 @@ extern "C" int mxb_select_tiles(mxb_handle_t c, const MxbProblem* problems, int 
     t.tile_n = pick_tile_n(p, k);
     t.tile_k = k.k_per_block;
     t.stages = mxb::GG_STAGES;
-    t.path = (p.a_bits == 16 && p.w_bits == 4 && p.M <= 16) ? 1 : 0;
+    t.path = (p.a_bits == 16 && p.w_bits == 4 && p.M <= 16 && p.K % 128 == 0) ? 1 : 0;
     // tensor time: tiles x k-slabs x 4 MMAs x (128*N/256) cycles each (B300_MICROARCH "tcgen05 floor"), spread over the SMs
     const double tiles = double((p.M + 127) / 128) * double((p.N + t.tile_n - 1) / t.tile_n);
     const double kb = double((p.K + k.k_per_block - 1) / k.k_per_block);

@@ -128,7 +128,8 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
     }
     S.m_arr[p] = m;
     S.row0[p] = r0;
-    S.prefix[p + 1] = ((m + GG_BM - 1) / GG_BM) * d.n_tiles;  // per-problem tile count, scanned below
+    // per-problem tile count, scanned below (problems routed to the streaming kernel contribute none)
+    S.prefix[p + 1] = d.path == 0 ? ((m + GG_BM - 1) / GG_BM) * d.n_tiles : 0;
   }
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < GG_STAGES; ++i) {
@@ -432,25 +433,35 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
         const int r_base = ct >> 1, hf = ct & 1;
         const float bias = w4 ? (sym ? 1031.f : 1024.f) : (sym ? 1151.f : 1024.f);
         const __half2 bias2 = __float2half2_rn(bias);
-        __half2 sc[2], zp[2];
-        for (int kb = 0; kb < kblocks; ++kb) {
-          if (kb % kpg == 0) {
-            const int g = kb / kpg;
+        __half2 sc[2], zp[2], sc_n[2], zp_n[2];
+        // scales of group g+1 are fetched while group g is converted (a global load on the critical path of every
+        // k-block made the converters, not the tensor cores, the bottleneck of the weight-only path)
+        auto load_scales = [&](int g) {
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-              const int n = n0 + r_base + 64 * j;
-              sc[j] = __float2half2_rn(0.f);
-              zp[j] = __float2half2_rn(0.f);
-              if (j < rows_per_thread && n < N) {
-                if (sym) {
-                  sc[j] = __half2half2(sb[static_cast<int64_t>(g) * N + n]);
-                } else {
-                  __half2 t = *reinterpret_cast<const __half2*>(sb + (static_cast<int64_t>(g) * N + n) * 2);
-                  sc[j] = __half2half2(__low2half(t));
-                  zp[j] = __half2half2(__high2half(t));
-                }
+          for (int j = 0; j < 2; ++j) {
+            const int n = n0 + r_base + 64 * j;
+            sc_n[j] = __float2half2_rn(0.f);
+            zp_n[j] = __float2half2_rn(0.f);
+            if (j < rows_per_thread && n < N && g * kpg < kblocks) {
+              if (sym) {
+                sc_n[j] = __half2half2(sb[static_cast<int64_t>(g) * N + n]);
+              } else {
+                __half2 t = *reinterpret_cast<const __half2*>(sb + (static_cast<int64_t>(g) * N + n) * 2);
+                sc_n[j] = __half2half2(__low2half(t));
+                zp_n[j] = __half2half2(__high2half(t));
               }
             }
+          }
+        };
+        load_scales(0);
+        for (int kb = 0; kb < kblocks; ++kb) {
+          if (kb % kpg == 0) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              sc[j] = sc_n[j];
+              zp[j] = zp_n[j];
+            }
+            load_scales(kb / kpg + 1);
           }
           mbar_wait(&S.cfull[stage], (cphase_bits >> stage) & 1);
           cphase_bits ^= 1u << stage;

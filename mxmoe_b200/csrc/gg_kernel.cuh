@@ -47,8 +47,12 @@ struct alignas(128) DevProblem {
   int32_t gsize, sym;
   int32_t scale_a_ld;  // fp16 elements per row of scale_a (1 or K/gsize)
   int32_t kb_per_group; // k-blocks per quantization group (EPI_INT_GROUP / grouped W-only)
+  int32_t path;         // 0 = tcgen05 persistent GroupGEMM, 1 = HBM-streaming w4a16 kernel (w4a16_stream.cu)
+  const void* A_ptr;    // raw operand pointers for the streaming path
+  const void* B_ptr;
+  int64_t lda;          // elements per row of A
 };
-static_assert(sizeof(DevProblem) == 384, "DevProblem layout");
+static_assert(sizeof(DevProblem) == 512, "DevProblem layout");
 
 constexpr int GG_MAXP = 256;       // problems per launch (host splits longer lists)
 constexpr int GG_THREADS = 384;    // 12 warps: TMA, MMA, TMEM-alloc, spare, 4 epilogue, 4 converter
@@ -64,6 +68,8 @@ constexpr int GG_SMEM_BYTES = 1024 /*align slack*/ + GG_STAGES * GG_STAGE_BYTES 
                               (3 * GG_MAXP + 4) * 4;
 
 void gg_launch(const DevProblem* probs, int P, int grid, cudaStream_t stream);
+void w4a16_stream_launch(const DevProblem* probs, int P, const int32_t* task_prefix_dev, int total_tasks, int classes, cudaStream_t st);
+int w4a16_stream_rows_per_task();
 int gg_configure();  // cudaFuncSetAttribute(max dynamic smem); returns cudaError_t as int
 
 }  // namespace mxb
