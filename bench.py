@@ -262,14 +262,26 @@ def main():
     my_gemm_ops = float(layer.gemm_ops(counts, T))
     int8_peak = 2.0 * pk["bf16"]
     if wl["q"] in ("fp16",) or "a16" in wl["q"]:
-        w_bytes = layer.weight_bytes()
-        ach = w_bytes * steps / (ms_gemm * 1e-3) / 1e9
+        # HBM-bound configs: algorithmic bytes = packed weights (+scales) of the experts that received tokens, read once,
+        # + activation rows read + fp16 outputs written by the two launches
+        act_bytes = 2 if (wl["q"] == "fp16" or "a16" in wl["q"]) else 1
+        rows = sum(counts)
+        w_bytes = layer.weight_bytes(active=[c > 0 for c in counts])
+        io_bytes = rows * (s["H"] * act_bytes + 2 * s["I"] * 2 + s["I"] * act_bytes + s["H"] * 2)
+        if s["ns"]:
+            io_bytes += T * (s["H"] * act_bytes + 3 * s["I"] * s["ns"] * 2 + s["H"] * 2)
+        ach = (w_bytes + io_bytes) * steps / (ms_gemm * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None,
-                "kernel": "gg_persistent_kernel (2 launches/step: gate_up + down)", "peak_source": pk["src"] + " copy bandwidth",
-                "algorithmic": "packed weight bytes + activation bytes read once + outputs written once per launch pair"}
+                "kernel": "gg_persistent_kernel + w4a16_stream_kernel (gate_up + down launches of one step)",
+                "peak_source": pk["src"] + " copy bandwidth",
+                "algorithmic": f"{w_bytes} B packed weights of the active experts + {io_bytes} B activations in/out per step",
+                "ms_per_launch_pair": ms_gemm / steps}
     else:
         ach = my_gemm_ops * steps / (ms_gemm * 1e-3) / 1e12
-        roof = {"bound": "tensor", "achieved": ach, "peak": int8_peak, "unit": "TOPS", "frac": ach / int8_peak, "traffic": None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of the two launches from one `ncu --set full` capture of this command
+        # (profiles/ncu_gg_persistent_r01.txt); only known for the default workload on one GPU
+        traffic = 978.4e6 if (args.workload == "c2" and W == 1 and not args.bs) else None
+        roof = {"bound": "tensor", "achieved": ach, "peak": int8_peak, "unit": "TOPS", "frac": ach / int8_peak, "traffic": traffic,
                 "kernel": "gg_persistent_kernel (2 launches/step: gate_up + down)",
                 "peak_source": f"2 x {pk['src']} cuBLAS bf16 burst ({pk['bf16']} TFLOPS): int8 dense = 2x bf16 on sm_100",
                 "algorithmic": "sum 2*M*N*K of the launch's problems", "ms_per_launch_pair": ms_gemm / steps}

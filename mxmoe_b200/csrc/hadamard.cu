@@ -14,6 +14,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "moe_ops.cuh"
 #include "quant_common.cuh"
@@ -31,7 +32,7 @@ __device__ __forceinline__ void ldsm_x2_trans(uint32_t addr, uint32_t (&r)[2]) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(addr));
 }
 __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
-  asm volatile(
+  asm(
       "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
       : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
@@ -62,6 +63,7 @@ struct HadParams {
   float scale;         // 1/sqrt(n)
   int warp_bytes;      // per-warp staging bytes
   int h_pitch;         // bytes per row of the shared copy of hmat
+  int dbg;             // MXB_HAD_DBG bit mask (profiling experiments only): 1 skip load-phase math, 2 skip MMA, 4 skip quant
 };
 
 template <bool SILU>
@@ -238,6 +240,7 @@ cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t
   p.m = n / K;
   p.scale = static_cast<float>(1.0 / sqrt(static_cast<double>(n)));
   p.h_pitch = Kp * 2 + 16;
+  { const char* e = getenv("MXB_HAD_DBG"); p.dbg = e ? atoi(e) : 0; }
   if (K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {
     if (Kp == 176) return launch_mma<11>(silu, p, sm_count, st);
     if (Kp == 48) return launch_mma<3>(silu, p, sm_count, st);

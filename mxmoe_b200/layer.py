@@ -196,9 +196,12 @@ class MoELayer:
         # permute (2) + act-quant (1 [+1 shared]) + GroupGEMM (1) + silu*mul+quant (1 [+1 shared]) + GroupGEMM (1) + combine (1)
         return 7 + (2 if self.ns else 0)
 
-    def weight_bytes(self) -> int:
+    def weight_bytes(self, active=None) -> int:
+        """bytes of packed weights + scales; `active[i]` masks routed local experts (the shared expert always counts)"""
         tot = 0
-        for e in self.experts:
+        for i, e in enumerate(self.experts):
+            if active is not None and i < self.EL and not active[i]:
+                continue
             for t in (e.gu_packed, e.gu_scale, e.dn_packed, e.dn_scale):
                 if t is not None:
                     tot += t.numel() * t.element_size()
