@@ -94,6 +94,13 @@ int mxb_destroy(mxb_handle_t h);
 const char* mxb_last_error(void);
 int mxb_sm_count(mxb_handle_t h);
 const char* mxb_version(void);
+/* Which GroupGEMM kernel serves mxb_group_gemm*: 0 (default) = chosen per problem list — the CTA-pair kernel
+ * (tcgen05 cta_group::2, 256 weight rows x <=256 tokens per tile) when every problem is fp16 / w8a8 / w4a4 with
+ * g-1 scales and no explicit tile_n, else the single-CTA kernel; 1 = always the single-CTA kernel; 2 = the
+ * CTA-pair kernel, MXB_EINVAL if the list holds a problem it does not cover.  The reference makes the
+ * corresponding choice at code-generation time from tile_config.json (mxmoe/kernels/tile_config.py:330-610).
+ * The environment variable MXB_GEMM_PATH sets the initial value. */
+int mxb_set_gemm_path(mxb_handle_t h, int path);
 
 /* ---- piece (3)+(4): one launch over a mixed-precision problem list ---- */
 /* `problems` is a HOST array.  Plans (tile tables, tensor maps) are cached in the handle keyed by its content. */

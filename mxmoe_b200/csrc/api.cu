@@ -10,6 +10,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <unordered_map>
@@ -57,6 +58,7 @@ struct Plan {
   mxb::DevProblem* dev = nullptr;  // device array, capacity GG_MAXP per chunk list
   int32_t* task_prefix = nullptr;  // [P+1] slab prefix of the problems routed to the streaming kernel
   int stream_tasks = 0, tc_problems = 0, stream_classes = 0;
+  bool paired = false;             // problems are encoded for gg_pair_kernel (CTA pairs, cta_group::2)
   size_t cap = 0;
   uint64_t last_use = 0;
 };
@@ -73,6 +75,7 @@ struct DevTable {  // small constant tables mirrored on the device, keyed by con
 struct mxb_context {
   int device = 0;
   int sm_count = 0;
+  int gemm_path = 0;  // 0 = choose per problem list, 1 = single-CTA kernel, 2 = CTA-pair kernel (error if not eligible)
   EncodeTiledFn encode = nullptr;
   std::vector<Plan> plans;
   std::vector<DevTable> tables;
@@ -153,7 +156,17 @@ int pick_tile_n(const MxbProblem& p, const KindInfo& k) {
   return bn;
 }
 
-int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, mxb::DevProblem* d) {
+// Problems the CTA-pair kernel covers: per-token / per-channel scaled integer kinds and plain fp16, on the
+// tensor-core path, with no explicit tile_n request (tile_n addresses the single-CTA kernel's UMMA N).
+bool pair_eligible(const MxbProblem& p) {
+  KindInfo k = {};
+  if (classify(p, &k) != MXB_OK) return false;
+  if (p.tile_n != 0) return false;
+  if (k.epi == mxb::EPI_INT_GROUP) return false;
+  return k.conv == mxb::CONV_NONE || k.conv == mxb::CONV_W4_I8;
+}
+
+int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, bool paired, mxb::DevProblem* d) {
   memset(d, 0, sizeof *d);
   KindInfo k = {};
   int rc = classify(p, &k);
@@ -170,7 +183,7 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, mxb
   if (!p.A || !p.B || !p.C) return fail(MXB_EINVAL, "null operand pointer");
   if (k.epi != mxb::EPI_F32 && (!p.scale_a || !p.scale_b)) return fail(MXB_EINVAL, "quantized problem without scales");
   if (k.conv >= mxb::CONV_W4_F16 && !p.scale_b) return fail(MXB_EINVAL, "weight-only problem without scale_b");
-  const int bn = pick_tile_n(p, k);
+  const int bn = paired ? 256 : pick_tile_n(p, k);
   const int64_t lda = p.lda > 0 ? p.lda : p.K;
   d->scale_a = static_cast<const __half*>(p.scale_a);
   d->scale_b = static_cast<const __half*>(p.scale_b);
@@ -201,24 +214,28 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, mxb
   // tile_config.py:330-610): 4-bit weight-only problems with at most 16 rows stream through w4a16_stream.cu.
   // With device-resident M the row capacity of the shared buffer decides (decode batches).
   const int m_cap = p.m_range ? (p.M <= 512 ? 16 : p.M) : p.M;
-  d->path = (k.conv == mxb::CONV_W4_F16 && m_cap <= 16 && p.K % 128 == 0 && p.tile_n == 0) ? 1 : 0;
+  d->path = (!paired && k.conv == mxb::CONV_W4_F16 && m_cap <= 16 && p.K % 128 == 0 && p.tile_n == 0) ? 1 : 0;
   if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k
   else if (k.conv >= mxb::CONV_W4_F16) d->kb_per_group = p.gsize == 128 ? 2 : d->kblocks;  // fp16 slabs hold 64 k
   else d->kb_per_group = d->kblocks;
   if (d->kb_per_group < 1) d->kb_per_group = 1;
   const uint32_t cfmt = k.mma_kind == mxb::MMA_I8 ? 2u : 1u;
   const uint32_t abfmt = k.mma_kind == mxb::MMA_I8 ? 1u : 0u;
-  d->idesc = (cfmt << 4) | (abfmt << 7) | (abfmt << 10) | ((uint32_t(bn) >> 3) << 17) | ((128u >> 4) << 24);
+  // pair kernel: UMMA M = 256 (weights), the token extent (UMMA N) is patched in per tile on the device
+  d->idesc = (cfmt << 4) | (abfmt << 7) | (abfmt << 10) |
+             (paired ? ((256u >> 4) << 24) : (((uint32_t(bn) >> 3) << 17) | ((128u >> 4) << 24)));
 
-  // A: [rows, K] of fp16 or int8, 128-byte swizzled box of 128 rows
+  // A (tokens): [rows, K] of fp16 or int8, 128-byte swizzled box of 128 rows (pair kernel: 32-row boxes, so a
+  // token tile of any multiple of 16 rows moves only the rows it needs)
   const CUtensorMapDataType adt = k.a_elsize == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
-  rc = encode_2d(c, &d->tmA, adt, k.a_elsize, p.A, p.K, p.M, lda * k.a_elsize, k.k_per_block, 128, true);
+  rc = encode_2d(c, &d->tmA, adt, k.a_elsize, p.A, p.K, p.M, lda * k.a_elsize, k.k_per_block, paired ? 32 : 128, true);
   if (rc) return rc;
+  const int wbox = paired ? 128 : bn;  // weight rows per TMA box (pair kernel: each CTA stages 128 of the tile's 256)
   if (k.conv == mxb::CONV_NONE) {
-    rc = encode_2d(c, &d->tmB, adt, k.a_elsize, p.B, p.K, p.N, uint64_t(p.K) * k.a_elsize, k.k_per_block, bn, true);
+    rc = encode_2d(c, &d->tmB, adt, k.a_elsize, p.B, p.K, p.N, uint64_t(p.K) * k.a_elsize, k.k_per_block, wbox, true);
   } else {
     const uint64_t row_bytes = uint64_t(p.K) * p.w_bits / 8;
-    rc = encode_2d(c, &d->tmB, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p.B, row_bytes, p.N, row_bytes, k.b_bytes_per_kb, bn, false);
+    rc = encode_2d(c, &d->tmB, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p.B, row_bytes, p.N, row_bytes, k.b_bytes_per_kb, wbox, false);
   }
   return rc;
 }
@@ -262,6 +279,7 @@ int device_table(mxb_context* c, const void* host, size_t bytes, cudaStream_t st
 int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* acc_out, cudaStream_t st, Plan** out) {
   uint64_t key = fnv1a(problems, sizeof(MxbProblem) * size_t(P));
   if (acc_out) key = fnv1a(acc_out, sizeof(int32_t*) * size_t(P), key ^ 0x9e3779b97f4a7c15ull);
+  key ^= uint64_t(c->gemm_path) * 0x632be59bd9b4e019ull;
   ++c->tick;
   for (auto& pl : c->plans)
     if (pl.key == key && pl.P == P) {
@@ -269,9 +287,14 @@ int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* 
       *out = &pl;
       return MXB_OK;
     }
+  // Kernel choice for the whole list (one launch): the CTA-pair kernel when every problem is one it covers.
+  bool paired = c->gemm_path != 1;
+  for (int i = 0; i < P && paired; ++i)
+    if (!(problems[i].M == 0 && !problems[i].m_range) && !pair_eligible(problems[i])) paired = false;
+  if (c->gemm_path == 2 && !paired) return fail(MXB_EINVAL, "gemm path 2 (CTA pairs) requested but the list holds a problem it does not cover");
   std::vector<mxb::DevProblem> host(static_cast<size_t>(P));
   for (int i = 0; i < P; ++i) {
-    int rc = build_dev_problem(c, problems[i], acc_out ? acc_out[i] : nullptr, &host[i]);
+    int rc = build_dev_problem(c, problems[i], acc_out ? acc_out[i] : nullptr, paired, &host[i]);
     if (rc) {
       std::string m = g_err;
       return fail(rc, "problem %d: %s", i, m.c_str());
@@ -310,6 +333,7 @@ int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* 
   slot->stream_tasks = tprefix[P];
   slot->tc_problems = tc_problems;
   slot->stream_classes = stream_classes;
+  slot->paired = paired;
   // pageable source: the runtime stages the bytes before returning, so `host` may die right after
   CU_OK(cudaMemcpyAsync(slot->dev, host.data(), sizeof(mxb::DevProblem) * size_t(P), cudaMemcpyHostToDevice, st));
   slot->key = key;
@@ -332,7 +356,8 @@ int group_gemm_impl(mxb_context* c, const MxbProblem* problems, int P, int32_t* 
   if (pl->tc_problems > 0) {
     for (int off = 0; off < P; off += mxb::GG_MAXP) {
       const int n = P - off < mxb::GG_MAXP ? P - off : mxb::GG_MAXP;
-      mxb::gg_launch(pl->dev + off, n, c->sm_count, st);
+      if (pl->paired) mxb::gg_pair_launch(pl->dev + off, n, c->sm_count, st);
+      else mxb::gg_launch(pl->dev + off, n, c->sm_count, st);
     }
   }
   CU_OK(cudaGetLastError());
@@ -370,6 +395,12 @@ int mxb_create(int device, mxb_handle_t* out) {
     delete c;
     return fail(MXB_ECUDA, "cudaFuncSetAttribute(max dynamic smem %d): %s", mxb::GG_SMEM_BYTES, cudaGetErrorString(e));
   }
+  e = static_cast<cudaError_t>(mxb::gg_pair_configure());
+  if (e != cudaSuccess) {
+    delete c;
+    return fail(MXB_ECUDA, "cudaFuncSetAttribute(max dynamic smem %d): %s", mxb::gg_pair_smem_bytes(), cudaGetErrorString(e));
+  }
+  if (const char* env = getenv("MXB_GEMM_PATH")) c->gemm_path = atoi(env);
   c->ws_bytes = 8u << 20;
   e = cudaMalloc(reinterpret_cast<void**>(&c->ws), c->ws_bytes);
   if (e != cudaSuccess) {
@@ -402,6 +433,13 @@ int mxb_destroy(mxb_handle_t c) {
 }
 
 int mxb_sm_count(mxb_handle_t c) { return c ? c->sm_count : 0; }
+
+int mxb_set_gemm_path(mxb_handle_t c, int path) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (path < 0 || path > 2) return fail(MXB_EINVAL, "gemm path %d (0 = auto, 1 = single-CTA kernel, 2 = CTA-pair kernel)", path);
+  c->gemm_path = path;
+  return MXB_OK;
+}
 
 int mxb_group_gemm(mxb_handle_t c, const MxbProblem* problems, int problem_count, void* stream) {
   return group_gemm_impl(c, problems, problem_count, nullptr, stream);

@@ -72,4 +72,12 @@ void w4a16_stream_launch(const DevProblem* probs, int P, const int32_t* task_pre
 int w4a16_stream_rows_per_task();
 int gg_configure();  // cudaFuncSetAttribute(max dynamic smem); returns cudaError_t as int
 
+// CTA-pair kernel (gg_pair_kernel.cu): tcgen05 cta_group::2, weights as the UMMA M operand, tokens as UMMA N.
+// DevProblem fields are read with the pair meaning: tmA = tokens with a 32-row box, tmB = weights with a 128-row
+// box, n_tiles = ceil(N / 256), idesc carries M = 256 and no N (the token extent is patched in per tile).
+void gg_pair_launch(const DevProblem* probs, int P, int grid, cudaStream_t stream);
+int gg_pair_configure();
+int gg_pair_smem_bytes();
+int gg_pair_stages();
+
 }  // namespace mxb

@@ -1,0 +1,415 @@
+// Piece (3), compute-bound form: the persistent grouped GEMM on CTA PAIRS (tcgen05 cta_group::2).
+//
+// Same contract as gg_kernel.cu (one launch over a problem list that mixes precisions; it replaces the
+// reference's generated `groupgemm_hz_fused_i_impl`, mxmoe/kernels/compose_kernel.py:153-224, its
+// mainloops cta_gemm.cuh:8,424 and the GlobalTileC epilogue mm_tile.cuh:445-496,610-662), but laid out
+// for what bounds a B200 at bs=8192: the L2 -> SM operand traffic and the 128-row token-tile waste of
+// MoE problems whose M is a few hundred rows.
+//
+//   * A cluster of 2 CTAs (one TPC) computes one 256 (weight rows) x NT (tokens) tile with
+//     `tcgen05.mma.cta_group::2`, UMMA M = 256.  The WEIGHTS are the UMMA "A" operand (128 rows per CTA)
+//     and the TOKENS the UMMA "B" operand (NT/2 rows per CTA): C^T = W * X^T.  With the operands swapped
+//     the token extent of a tile is the UMMA N, which is any multiple of 16 up to 256, so an expert
+//     with M rows is cut into ceil(M/256) equal tiles of ~M/ceil(M/256) tokens (<= 15 padded rows per
+//     tile) instead of 128-row tiles (the reference pads to BM=128/256, tile_config.py).
+//   * Per 128-byte K slab each CTA stages 16 KB of weights (8 KB when they are 4-bit) + <= 16 KB of
+//     tokens for a 128 x 256 slice of the output: 2/3 of the L2 traffic of the single-CTA 128 x 256 tile,
+//     and 32 KB stages leave room for a 6-deep ring (the single-CTA kernel has 3).
+//   * 4-bit weights land packed in the upper half of their own stage and are expanded IN PLACE by the
+//     converter warps (registers in between, one named barrier), so staging costs no extra smem.
+//   * Barriers: TMA bytes of both CTAs are counted on the leader's `full`; the leader's single MMA
+//     thread commits with a cluster multicast to `empty` / `tmem_full` of both CTAs; the epilogue and
+//     converter warps of the peer arrive remotely on the leader's `tmem_empty` / `conv`.
+//   * Epilogue: TMEM lane = weight row n, column = token.  The per-token scale is staged in smem, the
+//     per-channel scale lives in one register; the arithmetic (int32 -> float, times the fp16-rounded
+//     product sa*sb, one rounding to fp16) is the reference's, mm_tile.cuh:490,643.
+//
+// Supported here: fp16, w8a8 and w4a4 with per-token / per-channel scales (g-1).  Lists containing
+// group-wise or weight-only problems run on gg_kernel.cu.
+#include "gg_kernel.cuh"
+#include "ptx.cuh"
+
+namespace mxb {
+using namespace ptx;
+
+namespace {
+
+constexpr int GP_STAGES = 6;
+constexpr int GP_W_BYTES = 128 * 128;  // this CTA's 128 weight rows x 128 B
+constexpr int GP_T_BYTES = 128 * 128;  // this CTA's half of the token tile, <= 128 rows x 128 B
+constexpr int GP_STAGE_BYTES = GP_W_BYTES + GP_T_BYTES;
+constexpr int GP_PACKED_OFF = GP_W_BYTES / 2;  // 4-bit weights land in the upper half of the W region
+constexpr int GP_TBOX_ROWS = 32;               // token TMA box
+constexpr int GP_TBOX_BYTES = GP_TBOX_ROWS * 128;
+constexpr int GP_BT = 256;                     // max tokens per tile (UMMA N)
+constexpr int GP_BN = 256;                     // weight rows per tile (UMMA M across the pair)
+
+struct Smem {
+  uint8_t* stages;
+  uint64_t* full;        // [S] leader: token (and unconverted weight) bytes of both CTAs landed
+  uint64_t* empty;       // [S] each CTA: the pair's MMAs finished reading this stage (multicast commit)
+  uint64_t* conv;        // [S] leader: converter warps of both CTAs finished (8 arrivals)
+  uint64_t* cfull;       // [S] each CTA: its own packed weights landed
+  uint64_t* tmem_full;   // [2] each CTA (multicast commit)
+  uint64_t* tmem_empty;  // [2] leader: epilogue warps of both CTAs drained the accumulator (8 arrivals)
+  uint32_t* tmem_ptr;
+  __half* sa_stage;      // [2][256] per-token scales of the tile being drained
+  int32_t* prefix;       // [P+1]
+  int32_t* m_arr;        // [P]
+  int32_t* row0;         // [P]
+};
+
+constexpr int GP_BAR_BYTES = 512;
+constexpr int GP_SA_BYTES = 2 * GP_BT * 2;
+constexpr int GP_SMEM_BYTES = 1024 + GP_STAGES * GP_STAGE_BYTES + GP_BAR_BYTES + GP_SA_BYTES + (3 * GG_MAXP + 4) * 4;
+
+__device__ __forceinline__ Smem carve(uint8_t* raw) {
+  Smem s;
+  uint32_t a = smem_u32(raw);
+  uint8_t* base = raw + ((1024u - (a & 1023u)) & 1023u);
+  s.stages = base;
+  uint8_t* p = base + GP_STAGES * GP_STAGE_BYTES;
+  s.full = reinterpret_cast<uint64_t*>(p);
+  s.empty = s.full + GP_STAGES;
+  s.conv = s.empty + GP_STAGES;
+  s.cfull = s.conv + GP_STAGES;
+  s.tmem_full = s.cfull + GP_STAGES;
+  s.tmem_empty = s.tmem_full + 2;
+  s.tmem_ptr = reinterpret_cast<uint32_t*>(s.tmem_empty + 2);
+  s.sa_stage = reinterpret_cast<__half*>(p + GP_BAR_BYTES);
+  s.prefix = reinterpret_cast<int32_t*>(p + GP_BAR_BYTES + GP_SA_BYTES);
+  s.m_arr = s.prefix + GG_MAXP + 1;
+  s.row0 = s.m_arr + GG_MAXP;
+  return s;
+}
+
+// One tile of the walk: weight rows [n0, n0+256) x tokens [t0, t0+nt) of problem p.
+struct PairTile {
+  int p, n0, t0, nt;
+};
+
+// Static round-robin over the flattened (problem, n chunk, token chunk) list, token chunks fastest so that
+// consecutive tiles (running on neighbouring pairs at the same time) share one weight slab in L2.
+struct PairWalk {
+  const int32_t* prefix;
+  const int32_t* m_arr;
+  int tile, total, p, step;
+  __device__ PairWalk(const Smem& S, int P) : prefix(S.prefix), m_arr(S.m_arr), tile(cluster_id_x()), total(S.prefix[P]), p(0),
+                                              step(n_clusters_x()) {}
+  __device__ bool next(PairTile* t) {
+    if (tile >= total) return false;
+    while (tile >= prefix[p + 1]) ++p;
+    const int loc = tile - prefix[p];
+    const int M = m_arr[p];
+    const int tch = (M + GP_BT - 1) / GP_BT;               // token chunks
+    const int per = (((M + tch - 1) / tch) + 15) & ~15;    // tokens per chunk, equalised, multiple of 16
+    const int n_blk = loc / tch, t_blk = loc - n_blk * tch;
+    t->p = p;
+    t->n0 = n_blk * GP_BN;
+    t->t0 = t_blk * per;
+    t->nt = min(per, M - t->t0);
+    tile += step;
+    return true;
+  }
+};
+
+__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+}  // namespace
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pair_kernel(const DevProblem* __restrict__ probs, int P) {
+  extern __shared__ uint8_t smem_raw[];
+  Smem S = carve(smem_raw);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  // ---- device-side tile table (M may live in device memory: DevProblem::m_range)
+  for (int p = threadIdx.x; p < P; p += GG_THREADS) {
+    const DevProblem& d = probs[p];
+    int m = d.M, r0 = 0;
+    if (d.m_range != nullptr) {
+      r0 = d.m_range[0];
+      m = d.m_range[1] - r0;
+      if (m < 0) m = 0;
+    }
+    S.m_arr[p] = m;
+    S.row0[p] = r0;
+    S.prefix[p + 1] = ((m + GP_BT - 1) / GP_BT) * d.n_tiles;
+  }
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < GP_STAGES; ++i) {
+      mbar_init(&S.full[i], 1);
+      mbar_init(&S.empty[i], 1);
+      mbar_init(&S.conv[i], 8);
+      mbar_init(&S.cfull[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&S.tmem_full[i], 1);
+      mbar_init(&S.tmem_empty[i], 8);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc_pair(S.tmem_ptr, 512);
+    tmem_relinquish_pair();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    int carry = 0;
+    if (lane == 0) S.prefix[0] = 0;
+    for (int base = 0; base < P; base += 32) {
+      int idx = base + lane;
+      int v = idx < P ? S.prefix[idx + 1] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+      }
+      if (idx < P) S.prefix[idx + 1] = v + carry;
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // barrier inits of both CTAs are visible before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem_base = *S.tmem_ptr;
+
+  if (warp == 0) {
+    // ============================================================ TMA producer (one thread in EACH CTA)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      PairTile t;
+      for (PairWalk w(S, P); w.next(&t);) {
+        const DevProblem& d = probs[t.p];
+        const int nt16 = (t.nt + 15) & ~15;
+        const int half = nt16 >> 1;                         // token rows this CTA stages
+        const int boxes = (half + GP_TBOX_ROWS - 1) / GP_TBOX_ROWS;
+        const int trow = S.row0[t.p] + t.t0 + int(rank) * half;
+        const int wrow = t.n0 + int(rank) * 128;
+        const int kblocks = d.kblocks, a_kstep = d.a_kstep, b_kstep = d.b_kstep;
+        const bool has_conv = d.conv != CONV_NONE;
+        // bytes counted on the leader's `full`: the token boxes of both CTAs (+ both weight halves when unconverted)
+        const uint32_t tx_full = 2u * uint32_t(boxes) * GP_TBOX_BYTES + (has_conv ? 0u : 2u * GP_W_BYTES);
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&S.empty[stage], phase ^ 1);
+          uint8_t* sw = S.stages + stage * GP_STAGE_BYTES;
+          uint8_t* st = sw + GP_W_BYTES;
+          const uint32_t full_leader = mapa_u32(smem_u32(&S.full[stage]), 0);
+          if (leader) mbar_expect_tx(&S.full[stage], tx_full);
+          if (has_conv) {
+            mbar_expect_tx(&S.cfull[stage], GP_W_BYTES / 2);
+            tma_load_2d(sw + GP_PACKED_OFF, &d.tmB, &S.cfull[stage], kb * b_kstep, wrow);
+          } else {
+            tma_load_2d_pair(sw, &d.tmB, full_leader, kb * b_kstep, wrow);
+          }
+          for (int b = 0; b < boxes; ++b)
+            tma_load_2d_pair(st + b * GP_TBOX_BYTES, &d.tmA, full_leader, kb * a_kstep, trow + b * GP_TBOX_ROWS);
+          if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================================================ MMA issuer (one thread of the leader CTA)
+    if (leader && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0, conv_phase_bits = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      PairTile t;
+      for (PairWalk w(S, P); w.next(&t);) {
+        const DevProblem& d = probs[t.p];
+        const int kblocks = d.kblocks;
+        const int nt16 = (t.nt + 15) & ~15;
+        const uint32_t idesc = d.idesc | ((uint32_t(nt16) >> 3) << 17);
+        const bool is_i8 = d.mma_kind == MMA_I8;
+        const bool has_conv = d.conv != CONV_NONE;
+        mbar_wait(&S.tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * 256;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&S.full[stage], phase);
+          if (has_conv) {
+            mbar_wait(&S.conv[stage], (conv_phase_bits >> stage) & 1);
+            conv_phase_bits ^= 1u << stage;
+          }
+          tc_fence_after();
+          const uint32_t w_addr = smem_u32(S.stages + stage * GP_STAGE_BYTES);
+          const uint64_t da = umma_desc_sw128(w_addr);
+          const uint64_t db = umma_desc_sw128(w_addr + GP_W_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+            if (is_i8) umma_i8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+            else       umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+          }
+          umma_commit_pair(&S.empty[stage], 3);
+          if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_pair(&S.tmem_full[acc], 3);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ============================================================ epilogue (4 warps in EACH CTA; lane = weight row)
+    const int q = warp - 4;
+    const int et = threadIdx.x - 128;  // 0..127
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t tmem_empty_leader = mapa_u32(smem_u32(&S.tmem_empty[0]), 0);
+    PairTile t;
+    for (PairWalk w(S, P); w.next(&t);) {
+      const DevProblem& d = probs[t.p];
+      const int N = d.N;
+      const int n = t.n0 + int(rank) * 128 + q * 32 + lane;  // this thread's output column (weight row)
+      const bool n_ok = n < N;
+      const int epi = d.epi;
+      const int shift = d.acc_shift;
+      const int64_t ldc = d.ldc;
+      const int grow0 = S.row0[t.p] + t.t0;  // global row of the tile's first token
+      __half* sa_buf = S.sa_stage + acc * GP_BT;
+      __half2 sb2 = __float2half2_rn(1.f);
+      if (epi == EPI_INT_ROWCOL) {
+        // stage the tile's per-token scales (each thread 2 of them), fetch this lane's per-channel scale
+        const __half* sa = d.scale_a + grow0;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int c = et + i * 128;
+          sa_buf[c] = c < t.nt ? sa[c] : __float2half(0.f);
+        }
+        if (n_ok) sb2 = __half2half2(d.scale_b[n]);
+      }
+      // every tile, also the unscaled ones: keeps the four warps within one tile of each other, which is what makes
+      // the two-deep sa_stage buffer safe
+      named_bar_sync(2, 128);
+      __half* Cp = d.C + static_cast<int64_t>(grow0) * ldc + n;
+      int32_t* ao = d.acc_out != nullptr ? d.acc_out + static_cast<int64_t>(t.t0) * N + n : nullptr;
+      mbar_wait(&S.tmem_full[acc], acc_phase);
+      tc_fence_after();
+      for (int c = 0; c < t.nt; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + acc * 256 + c, v);
+        tmem_ld_wait();
+        const int valid = n_ok ? min(32, t.nt - c) : 0;
+        uint32_t h[16];
+        if (epi == EPI_F32) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) h[j] = pack_half2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+        } else {
+          if (ao != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < valid) ao[static_cast<int64_t>(c + j) * N] = static_cast<int32_t>(v[j]) >> shift;
+          }
+          const uint4* sap = reinterpret_cast<const uint4*>(sa_buf + c);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const uint4 s4 = sap[g];
+            const uint32_t sw[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const __half2 prod = __hmul2(*reinterpret_cast<const __half2*>(&sw[j]), sb2);
+              const float2 pf = __half22float2(prod);
+              const int a0 = static_cast<int32_t>(v[g * 8 + 2 * j]) >> shift;
+              const int a1 = static_cast<int32_t>(v[g * 8 + 2 * j + 1]) >> shift;
+              h[g * 4 + j] = pack_half2(__int2float_rn(a0) * pf.x, __int2float_rn(a1) * pf.y);
+            }
+          }
+        }
+        __half* cp = Cp + static_cast<int64_t>(c) * ldc;
+        if (valid == 32) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            st_global_b16(cp, static_cast<uint16_t>(h[j] & 0xFFFFu));
+            st_global_b16(cp + ldc, static_cast<uint16_t>(h[j] >> 16));
+            cp += 2 * ldc;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            if (2 * j < valid) st_global_b16(cp, static_cast<uint16_t>(h[j] & 0xFFFFu));
+            if (2 * j + 1 < valid) st_global_b16(cp + ldc, static_cast<uint16_t>(h[j] >> 16));
+            cp += 2 * ldc;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(tmem_empty_leader + acc * 8);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 8) {
+    // ============================================================ 4-bit weight converters (4 warps in EACH CTA)
+    const int ct = threadIdx.x - 256;  // 0..127
+    int stage = 0;
+    uint32_t cphase_bits = 0;
+    const uint32_t conv_leader = mapa_u32(smem_u32(&S.conv[0]), 0);
+    PairTile t;
+    for (PairWalk w(S, P); w.next(&t);) {
+      const DevProblem& d = probs[t.p];
+      const int kblocks = d.kblocks;
+      if (d.conv == CONV_NONE) {
+        stage = (stage + kblocks) % GP_STAGES;
+        continue;
+      }
+      for (int kb = 0; kb < kblocks; ++kb) {
+        mbar_wait(&S.cfull[stage], (cphase_bits >> stage) & 1);
+        cphase_bits ^= 1u << stage;
+        uint8_t* wfin = S.stages + stage * GP_STAGE_BYTES;
+        const uint8_t* wpk = wfin + GP_PACKED_OFF;
+        // packed slab: 128 rows x 64 B; a 16-byte item holds 32 k (low nibbles k..k+15, high nibbles k+16..k+31).
+        // Everything is read into registers before the first write: the expansion overwrites the packed bytes.
+        uint4 w4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w4[j] = *reinterpret_cast<const uint4*>(wpk + (ct + j * 128) * 16);
+        named_bar_sync(1, 128);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int i = ct + j * 128;
+          const int row = i >> 2, c = i & 3;
+          uint4 lo, hi;
+          lo.x = (w4[j].x << 4) & 0xF0F0F0F0u; hi.x = w4[j].x & 0xF0F0F0F0u;
+          lo.y = (w4[j].y << 4) & 0xF0F0F0F0u; hi.y = w4[j].y & 0xF0F0F0F0u;
+          lo.z = (w4[j].z << 4) & 0xF0F0F0F0u; hi.z = w4[j].z & 0xF0F0F0F0u;
+          lo.w = (w4[j].w << 4) & 0xF0F0F0F0u; hi.w = w4[j].w & 0xF0F0F0F0u;
+          const int sw = row & 7;
+          *reinterpret_cast<uint4*>(wfin + row * 128 + (((2 * c) ^ sw) << 4)) = lo;
+          *reinterpret_cast<uint4*>(wfin + row * 128 + (((2 * c + 1) ^ sw) << 4)) = hi;
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(conv_leader + stage * 8);
+        if (++stage == GP_STAGES) stage = 0;
+      }
+    }
+  }
+
+  // ---- teardown: nobody leaves while the peer may still read its smem / arrive on its barriers
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 512);
+  }
+}
+
+int gg_pair_configure() {
+  return static_cast<int>(cudaFuncSetAttribute(gg_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GP_SMEM_BYTES));
+}
+
+int gg_pair_smem_bytes() { return GP_SMEM_BYTES; }
+int gg_pair_stages() { return GP_STAGES; }
+
+void gg_pair_launch(const DevProblem* probs, int P, int grid, cudaStream_t stream) {
+  gg_pair_kernel<<<grid & ~1, GG_THREADS, GP_SMEM_BYTES, stream>>>(probs, P);
+}
+
+}  // namespace mxb

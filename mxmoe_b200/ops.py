@@ -53,6 +53,7 @@ EXPORTS = [
     ("mxb_last_error", C.c_char_p, []),
     ("mxb_sm_count", _I, [_P]),
     ("mxb_version", C.c_char_p, []),
+    ("mxb_set_gemm_path", _I, [_P, _I]),
     ("mxb_group_gemm", _I, [_P, C.POINTER(MxbProblem), _I, _P]),
     ("mxb_group_gemm_debug_acc", _I, [_P, C.POINTER(MxbProblem), _I, C.POINTER(_P), _P]),
     ("mxb_group_gemm_reflayout", _I, [_P] + [_P] * 14 + [_I, _P]),
@@ -154,6 +155,10 @@ class Handle:
     @property
     def sm_count(self) -> int:
         return self.lib.mxb_sm_count(self.h)
+
+    def set_gemm_path(self, path: int):
+        """0 = auto (CTA-pair kernel when the whole list is eligible), 1 = single-CTA kernel, 2 = CTA-pair kernel."""
+        self._check(self.lib.mxb_set_gemm_path(self.h, int(path)), "mxb_set_gemm_path")
 
     # ---------------------------------------------------------------- grouped GEMM
     def pack_problems(self, problems: Sequence[Problem]):

@@ -16,10 +16,23 @@ pytestmark = pytest.mark.gpu
 REL_TOL = 1e-3  # north_star: max relative error for fp16 outputs
 
 
-@pytest.fixture(scope="module")
-def H():
+@pytest.fixture(scope="module", params=["auto", "single_cta"])
+def H(request):
+    """Every test runs twice: with the kernel chosen per list (the CTA-pair kernel where it is eligible) and with
+    the single-CTA kernel forced, so both implementations stay under the same parity bar."""
     from mxmoe_b200 import ops
-    return ops.Handle(0)
+    h = ops.Handle(0)
+    h.set_gemm_path(0 if request.param == "auto" else 1)
+    return h
+
+
+@pytest.fixture(scope="module")
+def HP():
+    """CTA-pair kernel forced: an ineligible list is an error instead of a silent switch of kernels."""
+    from mxmoe_b200 import ops
+    h = ops.Handle(0)
+    h.set_gemm_path(2)
+    return h
 
 
 def dev(a, dtype=None):
@@ -249,3 +262,84 @@ def test_many_tiles_per_cta_mixed_kinds(H):
         else:
             err = (got.double() - ref).abs().max().item() / ref.abs().max().item()
             assert err <= REL_TOL, f"problem {i}: rel err {err}"
+
+
+@pytest.mark.parametrize("w_bits", [16, 8, 4])
+@pytest.mark.parametrize("M", [1, 15, 16, 17, 100, 255, 256, 257, 513, 546])
+def test_pair_kernel_ragged_tokens(HP, w_bits, M):
+    """CTA-pair kernel (cta_group::2, tokens on the UMMA N axis): token extents around every tiling edge
+    (multiples of 16, the 256-token tile, equalised chunks), N with a tail (384 = 256 + 128), K = 1408 (11 slabs,
+    so the 6-deep ring wraps at an odd count)."""
+    from mxmoe_b200 import ops
+    rng = np.random.default_rng(w_bits * 100 + M)
+    N, K = 384, 1408
+    p, ref, acc = make_problem(ops, rng, M, N, K, w_bits, w_bits, -1, True)
+    if acc is None:
+        HP.group_gemm([p])
+        check([p], [ref], [None])
+    else:
+        buf = torch.zeros(M * N, dtype=torch.int32, device="cuda")
+        HP.group_gemm([p], acc_out=[buf])
+        check([p], [ref], [acc], [buf])
+
+
+def test_pair_kernel_many_tiles_mixed_kinds(HP):
+    """Every pair walks many tiles whose kinds alternate (in-place converted w4a4 / w8a8 / fp16) over shared buffers
+    with DEVICE-resident row ranges, including empty experts: the ring, the remote converter / epilogue barriers and
+    both TMEM accumulators wrap many times.  int32 accumulators bit-exact against float64 matmuls on the device."""
+    from mxmoe_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(11)
+    E, N, K = 24, 1280, 640
+    Ms = [0 if e % 7 == 3 else 40 + 97 * e for e in range(E)]
+    offs = np.concatenate([[0], np.cumsum(Ms)]).astype(np.int32)
+    tot = int(offs[-1])
+    d_offs = dev(offs)
+    qa8 = torch.randint(-127, 128, (tot, K), generator=g, device="cuda", dtype=torch.int32)
+    qa4 = torch.randint(-7, 8, (tot, K), generator=g, device="cuda", dtype=torch.int32)
+    Af = (torch.rand(tot, K, generator=g, device="cuda") * 2 - 1).half()
+    A8, A4 = qa8.to(torch.int8), qa4.to(torch.int8)
+    ones_m = torch.ones(tot, dtype=torch.float16, device="cuda")
+    ones_n = torch.ones(N, dtype=torch.float16, device="cuda")
+    Cb = torch.full((tot, N), float("nan"), dtype=torch.float16, device="cuda")
+    probs, accs, refs, keep = [], [], [], []
+    for e in range(E):
+        kind = e % 3
+        r = slice(int(offs[e]), int(offs[e + 1]))
+        if kind == 2:
+            Wt = (torch.rand(N, K, generator=g, device="cuda") * 2 - 1).half()
+            keep.append(Wt)
+            probs.append(ops.Problem(Af, Wt, Cb, tot, N, K, m_range=d_offs[e:e + 2]))
+            accs.append(None)
+            refs.append(("f16", Af[r].double() @ Wt.double().T))
+            continue
+        bits = 4 if kind == 0 else 8
+        hi = (1 << (bits - 1)) - 1
+        qw = torch.randint(-hi, hi + 1, (N, K), generator=g, device="cuda", dtype=torch.int32)
+        B = qw.to(torch.int8) if bits == 8 else dev(O.pack_wxax_native(qw.cpu().numpy(), 4))
+        keep.append(B)
+        acc = torch.zeros(max(Ms[e], 1), N, dtype=torch.int32, device="cuda")
+        probs.append(ops.Problem(A8 if bits == 8 else A4, B, Cb, tot, N, K, bits, bits, -1, True, scale_a=ones_m, scale_b=ones_n,
+                                 m_range=d_offs[e:e + 2]))
+        accs.append(acc)
+        refs.append(("int", ((qa8 if bits == 8 else qa4)[r].double() @ qw.double().T).to(torch.int32)))
+    arr = HP.pack_problems(probs)
+    for _ in range(3):  # repeated launches reuse the plan; results must not depend on leftover smem / TMEM state
+        HP.group_gemm(arr, acc_out=accs)
+    torch.cuda.synchronize()
+    for e, (kind, ref) in enumerate(refs):
+        if Ms[e] == 0:
+            continue
+        r = slice(int(offs[e]), int(offs[e + 1]))
+        if kind == "int":
+            assert torch.equal(accs[e][:Ms[e]], ref), f"expert {e}: int32 accumulators differ"
+        else:
+            err = (Cb[r].double() - ref).abs().max().item() / ref.abs().max().item()
+            assert err <= REL_TOL, f"expert {e}: rel err {err}"
+
+
+def test_pair_kernel_rejects_ineligible_list(HP):
+    from mxmoe_b200 import ops
+    rng = np.random.default_rng(3)
+    p, _, _ = make_problem(ops, rng, 64, 128, 256, 4, 4, 128, True)
+    with pytest.raises(ops.MxbError, match="CTA pairs"):
+        HP.group_gemm([p])

@@ -24,6 +24,10 @@ def main():
     B16 = (torch.rand(N, K, device=dev) - 0.5).half()
     sbw = torch.ones(K // 128 * N * 2, dtype=torch.float16, device=dev)
     cases = []
+    # tile_n = 0 on an eligible problem -> CTA-pair kernel (cta_group::2)
+    cases.append(("w8a8 pair", ops.Problem(A8, B8, C, M, N, K, 8, 8, -1, True, scale_a=sa, scale_b=sb)))
+    cases.append(("w4a4 pair", ops.Problem(A8, B4, C, M, N, K, 4, 4, -1, True, scale_a=sa, scale_b=sb)))
+    cases.append(("fp16 pair", ops.Problem(A16, B16, C, M, N, K)))
     for bn in (256, 128, 64):
         cases.append((f"w8a8 bn{bn}", ops.Problem(A8, B8, C, M, N, K, 8, 8, -1, True, scale_a=sa, scale_b=sb, tile_n=bn)))
     for bn in (256, 128, 64):
