@@ -230,6 +230,10 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   const CUtensorMapDataType adt = k.a_elsize == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
   rc = encode_2d(c, &d->tmA, adt, k.a_elsize, p.A, p.K, p.M, lda * k.a_elsize, k.k_per_block, paired ? 32 : 128, true);
   if (rc) return rc;
+  if (paired) {
+    rc = encode_2d(c, &d->tmA2, adt, k.a_elsize, p.A, p.K, p.M, lda * k.a_elsize, k.k_per_block, 128, true);
+    if (rc) return rc;
+  }
   const int wbox = paired ? 128 : bn;  // weight rows per TMA box (pair kernel: each CTA stages 128 of the tile's 256)
   if (k.conv == mxb::CONV_NONE) {
     rc = encode_2d(c, &d->tmB, adt, k.a_elsize, p.B, p.K, p.N, uint64_t(p.K) * k.a_elsize, k.k_per_block, wbox, true);

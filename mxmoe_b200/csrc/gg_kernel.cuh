@@ -51,8 +51,9 @@ struct alignas(128) DevProblem {
   const void* A_ptr;    // raw operand pointers for the streaming path
   const void* B_ptr;
   int64_t lda;          // elements per row of A
+  CUtensorMap tmA2;     // pair kernel only: tokens with a 128-row box (tmA has the 32-row box for ragged tiles)
 };
-static_assert(sizeof(DevProblem) == 512, "DevProblem layout");
+static_assert(sizeof(DevProblem) == 640, "DevProblem layout");
 
 constexpr int GG_MAXP = 256;       // problems per launch (host splits longer lists)
 constexpr int GG_THREADS = 384;    // 12 warps: TMA, MMA, TMEM-alloc, spare, 4 epilogue, 4 converter

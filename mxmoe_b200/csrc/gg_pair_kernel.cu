@@ -180,44 +180,58 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
   tc_fence_after();
   const uint32_t tmem_base = *S.tmem_ptr;
 
-  if (warp == 0) {
-    // ============================================================ TMA producer (one thread in EACH CTA)
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      PairTile t;
-      for (PairWalk w(S, P); w.next(&t);) {
-        const DevProblem& d = probs[t.p];
-        const int nt16 = (t.nt + 15) & ~15;
-        const int half = nt16 >> 1;                         // token rows this CTA stages
-        const int boxes = (half + GP_TBOX_ROWS - 1) / GP_TBOX_ROWS;
-        const int trow = S.row0[t.p] + t.t0 + int(rank) * half;
-        const int wrow = t.n0 + int(rank) * 128;
-        const int kblocks = d.kblocks, a_kstep = d.a_kstep, b_kstep = d.b_kstep;
-        const bool has_conv = d.conv != CONV_NONE;
-        // bytes counted on the leader's `full`: the token boxes of both CTAs (+ both weight halves when unconverted)
-        const uint32_t tx_full = 2u * uint32_t(boxes) * GP_TBOX_BYTES + (has_conv ? 0u : 2u * GP_W_BYTES);
-        for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&S.empty[stage], phase ^ 1);
-          uint8_t* sw = S.stages + stage * GP_STAGE_BYTES;
-          uint8_t* st = sw + GP_W_BYTES;
-          const uint32_t full_leader = mapa_u32(smem_u32(&S.full[stage]), 0);
-          if (leader) mbar_expect_tx(&S.full[stage], tx_full);
-          if (has_conv) {
+  if (warp == 0 || warp == 3) {
+    // ============================================================ TMA producers (in EACH CTA): warp 0 tokens, warp 3 weights.
+    // The whole warp walks the tiles converged and one elected lane issues: with a single-thread region the compiler
+    // wraps every UTMALDG in a uniform-register "waterfall" loop, and one thread issuing 5 loads per stage was the
+    // limiter of the first version of this kernel (ncu: producer busy 64 % of the time, converters starved).
+    const bool tokens = warp == 0;
+    int stage = 0;
+    uint32_t phase = 0;
+    PairTile t;
+    for (PairWalk w(S, P); w.next(&t);) {
+      const DevProblem& d = probs[t.p];
+      const int nt16 = (t.nt + 15) & ~15;
+      const int half = nt16 >> 1;  // token rows this CTA stages
+      // one 128-row box when (nearly) all of it is needed, else 32-row boxes: a ragged tile moves only its own rows
+      const bool big = half > 96;
+      const int boxes = big ? 1 : (half + GP_TBOX_ROWS - 1) / GP_TBOX_ROWS;
+      const uint32_t tok_bytes = big ? uint32_t(GP_T_BYTES) : uint32_t(boxes) * GP_TBOX_BYTES;
+      const int trow = S.row0[t.p] + t.t0 + int(rank) * half;
+      const int wrow = t.n0 + int(rank) * 128;
+      const int kblocks = d.kblocks, a_kstep = d.a_kstep, b_kstep = d.b_kstep;
+      const bool has_conv = d.conv != CONV_NONE;
+      // bytes counted on the leader's `full`: the token boxes of both CTAs (+ both weight halves when unconverted)
+      const uint32_t tx_full = 2u * tok_bytes + (has_conv ? 0u : 2u * GP_W_BYTES);
+      const CUtensorMap* tmT = big ? &d.tmA2 : &d.tmA;
+      for (int kb = 0; kb < kblocks; ++kb) {
+        mbar_wait(&S.empty[stage], phase ^ 1);
+        uint8_t* sw = S.stages + stage * GP_STAGE_BYTES;
+        const uint32_t full_leader = mapa_u32(smem_u32(&S.full[stage]), 0);
+        if (elect_one()) {
+          if (tokens) {
+            if (leader) mbar_expect_tx(&S.full[stage], tx_full);
+            uint8_t* st = sw + GP_W_BYTES;
+            if (big) {
+              tma_load_2d_pair(st, tmT, full_leader, kb * a_kstep, trow);
+            } else {
+              for (int b = 0; b < boxes; ++b)
+                tma_load_2d_pair(st + b * GP_TBOX_BYTES, tmT, full_leader, kb * a_kstep, trow + b * GP_TBOX_ROWS);
+            }
+          } else if (has_conv) {
             mbar_expect_tx(&S.cfull[stage], GP_W_BYTES / 2);
             tma_load_2d(sw + GP_PACKED_OFF, &d.tmB, &S.cfull[stage], kb * b_kstep, wrow);
           } else {
             tma_load_2d_pair(sw, &d.tmB, full_leader, kb * b_kstep, wrow);
           }
-          for (int b = 0; b < boxes; ++b)
-            tma_load_2d_pair(st + b * GP_TBOX_BYTES, &d.tmA, full_leader, kb * a_kstep, trow + b * GP_TBOX_ROWS);
-          if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    // ============================================================ MMA issuer (one thread of the leader CTA)
-    if (leader && lane == 0) {
+    // ============================================================ MMA issuer (leader CTA; warp converged, one elected lane issues)
+    if (leader) {
       int stage = 0;
       uint32_t phase = 0, conv_phase_bits = 0;
       int acc = 0;
@@ -243,16 +257,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
           const uint32_t w_addr = smem_u32(S.stages + stage * GP_STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(w_addr);
           const uint64_t db = umma_desc_sw128(w_addr + GP_W_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-            if (is_i8) umma_i8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
-            else       umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+            for (int k = 0; k < 4; ++k) {
+              const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+              if (is_i8) umma_i8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+              else       umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+            }
+            umma_commit_pair(&S.empty[stage], 3);
+            if (kb == kblocks - 1) umma_commit_pair(&S.tmem_full[acc], 3);
           }
-          umma_commit_pair(&S.empty[stage], 3);
+          __syncwarp();
           if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit_pair(&S.tmem_full[acc], 3);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
