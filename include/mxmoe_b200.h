@@ -72,8 +72,17 @@ typedef struct MxbProblem {
   int32_t M, N, K;
   int32_t a_bits, w_bits, gsize, sym; /* gsize -1 = per-channel/per-token */
   int32_t tile_n;                     /* 0 = let the selector choose; else 64/128/256 */
-  int32_t reserved;
+  int32_t flags;                      /* MXB_EPI_* bits, 0 = plain GEMM */
 } MxbProblem;
+
+/* Epilogue fusion of the step that follows the gate_up GEMM in the reference pipeline (silu_mul_then_quant,
+ * ref_bind.cu:595-757; HF act_fn(gate) * up): B holds the gate and up rows INTERLEAVED (row 2i = gate_i,
+ * row 2i+1 = up_i; scale_b interleaved the same way; mxb_interleave_gate_up converts the reference's
+ * [gate; up] order), N still counts all 2I rows, and C is fp16 [M, N/2] = silu(gate) * up with default
+ * ldc = N/2.  gate and up are first rounded to fp16 exactly as the unfused GEMM would store them, then combined
+ * with the arithmetic of mxb_silu_mul_quant, so the result is bit-identical to the two-step path.
+ * Served by the CTA-pair kernel only: a list that is not eligible for it (see mxb_set_gemm_path) is MXB_EINVAL. */
+#define MXB_EPI_SILU_MUL 1
 
 /* Per-expert activation quantization parameters for mxb_quant_act / mxb_silu_mul_quant
  * (the reference's qparams_per_exp tuples, ref_bind.cu:321,365). */
@@ -153,6 +162,10 @@ int mxb_quant_pack_weight(mxb_handle_t h, const void* W, int N, int K, int w_bit
  * -> native layout.  Scales already share the reference's permute_scale layout and need no conversion. */
 int mxb_repack_from_ref(mxb_handle_t h, const void* ref_packed, int N, int K, int w_bits, int a_bits, int sym,
                         void* packed, void* stream);
+/* Row interleave for MXB_EPI_SILU_MUL: src holds 2I rows of row_bytes bytes ([gate rows; up rows], the reference's
+ * fused gate_up order, gen_workload.py:84-93); dst row 2i = src row i, dst row 2i+1 = src row I+i.  Works on packed
+ * weight rows of any bit width and, with row_bytes = 2 (4 for asym pairs), on per-channel scale vectors. */
+int mxb_interleave_gate_up(mxb_handle_t h, const void* src, int I, int64_t row_bytes, void* dst, void* stream);
 int64_t mxb_packed_bytes(int N, int K, int w_bits);
 int64_t mxb_scale_elems(int N, int K, int w_bits, int a_bits, int gsize, int sym);
 

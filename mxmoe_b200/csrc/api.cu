@@ -163,6 +163,7 @@ bool pair_eligible(const MxbProblem& p) {
   if (classify(p, &k) != MXB_OK) return false;
   if (p.tile_n != 0) return false;
   if (k.epi == mxb::EPI_INT_GROUP) return false;
+  if ((p.flags & MXB_EPI_SILU_MUL) && p.N % 2 != 0) return false;
   return k.conv == mxb::CONV_NONE || k.conv == mxb::CONV_W4_I8;
 }
 
@@ -190,7 +191,11 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   d->C = static_cast<__half*>(p.C);
   d->acc_out = acc_out;
   d->m_range = p.m_range;
-  d->ldc = p.ldc > 0 ? p.ldc : p.N;
+  if (p.flags & ~MXB_EPI_SILU_MUL) return fail(MXB_EINVAL, "unknown problem flags 0x%x", p.flags);
+  if ((p.flags & MXB_EPI_SILU_MUL) && !paired)
+    return fail(MXB_EINVAL, "MXB_EPI_SILU_MUL is served by the CTA-pair kernel only (list not eligible, or gemm path 1)");
+  d->epi_flags = p.flags;
+  d->ldc = p.ldc > 0 ? p.ldc : ((p.flags & MXB_EPI_SILU_MUL) ? p.N / 2 : p.N);
   d->M = p.M;
   d->N = p.N;
   d->K = p.K;
@@ -654,6 +659,20 @@ int mxb_combine(mxb_handle_t c, const void* down_out, int H, const int32_t* slot
   if (T > 0 && (!down_out || !slot_of || !topk_w || !out)) return fail(MXB_EINVAL, "null pointer");
   CU_OK(cudaSetDevice(c->device));
   CU_OK(mxb::combine_launch(down_out, H, slot_of, topk_w, T, k, shared_out, out, static_cast<cudaStream_t>(stream)));
+  return MXB_OK;
+}
+
+int mxb_interleave_gate_up(mxb_handle_t c, const void* src, int I, int64_t row_bytes, void* dst, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (!src || !dst || I < 1 || row_bytes < 1 || src == dst) return fail(MXB_EINVAL, "bad argument");
+  CU_OK(cudaSetDevice(c->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const char* s8 = static_cast<const char*>(src);
+  char* d8 = static_cast<char*>(dst);
+  // two strided 2-D copies: gate rows to the even rows, up rows to the odd rows (offline weight path)
+  CU_OK(cudaMemcpy2DAsync(d8, 2 * row_bytes, s8, row_bytes, row_bytes, I, cudaMemcpyDeviceToDevice, st));
+  CU_OK(cudaMemcpy2DAsync(d8 + row_bytes, 2 * row_bytes, s8 + int64_t(I) * row_bytes, row_bytes, row_bytes, I,
+                          cudaMemcpyDeviceToDevice, st));
   return MXB_OK;
 }
 

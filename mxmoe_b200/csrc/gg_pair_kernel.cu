@@ -28,6 +28,7 @@
 // group-wise or weight-only problems run on gg_kernel.cu.
 #include "gg_kernel.cuh"
 #include "ptx.cuh"
+#include "quant_common.cuh"
 
 namespace mxb {
 using namespace ptx;
@@ -290,6 +291,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
       const int epi = d.epi;
       const int shift = d.acc_shift;
       const int64_t ldc = d.ldc;
+      const bool silu = (d.epi_flags & 1) != 0;
       const int grow0 = S.row0[t.p] + t.t0;  // global row of the tile's first token
       __half* sa_buf = S.sa_stage + acc * GP_BT;
       __half2 sb2 = __float2half2_rn(1.f);
@@ -339,6 +341,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
               h[g * 4 + j] = pack_half2(__int2float_rn(a0) * pf.x, __int2float_rn(a1) * pf.y);
             }
           }
+        }
+        if (silu) {
+          // Fused act_fn(gate) * up (MXB_EPI_SILU_MUL): even lanes hold gate_i, odd lanes up_i (interleaved weight rows).
+          // The pair swaps one value per two tokens; the even lane finishes token c+2j, the odd lane token c+2j+1, each
+          // from the fp16-rounded gate/up the unfused GEMM would have stored (silu_mul_h: quant_common.cuh).
+          const int odd = lane & 1;
+          __half* hp = d.C + static_cast<int64_t>(grow0 + c + odd) * ldc + (n >> 1);
+#pragma unroll
+          for (int j = 0; j < 16; j += 2) {
+            const uint32_t send = odd ? ((h[j] & 0xFFFFu) | (h[j + 1] << 16)) : ((h[j] >> 16) | (h[j + 1] & 0xFFFF0000u));
+            const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 1);
+#pragma unroll
+            for (int jj = 0; jj < 2; ++jj) {
+              const uint16_t own = odd ? static_cast<uint16_t>(h[j + jj] >> 16) : static_cast<uint16_t>(h[j + jj] & 0xFFFFu);
+              const uint16_t oth = static_cast<uint16_t>(jj ? (recv >> 16) : (recv & 0xFFFFu));
+              const __half g = __ushort_as_half(odd ? oth : own), u = __ushort_as_half(odd ? own : oth);
+              const __half r = __float2half_rn(silu_mul_h(g, u));
+              if (2 * (j + jj) + odd < valid) st_global_b16(hp, __half_as_ushort(r));
+              hp += 2 * ldc;
+            }
+          }
+          continue;
         }
         __half* cp = Cp + static_cast<int64_t>(c) * ldc;
         if (valid == 32) {

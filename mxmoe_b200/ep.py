@@ -90,7 +90,8 @@ class EPMoELayer(MoELayer):
         for s in range(self.W):
             for i, ew in enumerate(self.experts[:self.EL]):
                 mr = self.seg_offs[s * self.EL + i: s * self.EL + i + 2]
-                gu.append(self._problem(ew.q_gu, self.x_q8, self.x_f16, self.x_sc, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * I, H, mr))
+                gu.append(self._problem(ew.q_gu, self.x_q8, self.x_f16, self.x_sc, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * I, H, mr,
+                                        flags=ops.EPI_SILU_MUL if self.fused_silu else 0))
                 dn.append(self._problem(ew.q_dn, self.h_q8, self.h_f16, self.h_sc, ew.dn_packed, ew.dn_scale, self.dn_out, R, H, I, mr))
         self._gu_routed, self._dn_routed = gu, dn
         self._seg_actq_gu = [(e.q_gu.a_bits, e.q_gu.a_gsize) for _ in range(self.W) for e in self.experts[:self.EL]]
@@ -135,11 +136,20 @@ class EPMoELayer(MoELayer):
             if s.q_gu.a_bits < 16:
                 h.quant_act(x, None, T, None, [(s.q_gu.a_bits, s.q_gu.a_gsize)], False, self.sx_q8, None, self.sx_sc)
         h.group_gemm(self._gu_arr)
-        h.silu_mul_quant(self.gu_out, n_recv, self.seg_offs, self._seg_actq_dn, self.hadamard_down, self.h_q8, self.h_f16, self.h_sc)
-        if self.ns:
-            s = self.experts[-1]
-            h.silu_mul_quant(self.s_gu, T, None, [(s.q_dn.a_bits, s.q_dn.a_gsize)], self.hadamard_down, self.sh_q8, self.sh_f16,
-                             self.sh_sc)
+        if self.fused_silu:  # the gate_up epilogue already wrote silu(gate)*up
+            if not self.h_direct:
+                h.quant_act(self.gu_out, None, n_recv, self.seg_offs, self._seg_actq_dn, self.hadamard_down, self.h_q8, self.h_f16,
+                            self.h_sc)
+            if self.ns and not self.sh_direct:
+                s = self.experts[-1]
+                h.quant_act(self.s_gu, None, T, None, [(s.q_dn.a_bits, s.q_dn.a_gsize)], self.hadamard_down, self.sh_q8, self.sh_f16,
+                            self.sh_sc)
+        else:
+            h.silu_mul_quant(self.gu_out, n_recv, self.seg_offs, self._seg_actq_dn, self.hadamard_down, self.h_q8, self.h_f16, self.h_sc)
+            if self.ns:
+                s = self.experts[-1]
+                h.silu_mul_quant(self.s_gu, T, None, [(s.q_dn.a_bits, s.q_dn.a_gsize)], self.hadamard_down, self.sh_q8, self.sh_f16,
+                                 self.sh_sc)
         h.group_gemm(self._dn_arr)
 
     # ------------------------------------------------------------------ bench helpers
@@ -150,4 +160,7 @@ class EPMoELayer(MoELayer):
         return self._last_seg.reshape(self.W, self.EL).sum(0).tolist()
 
     def launches_per_step(self) -> int:
-        return 8 + (2 if self.ns else 0) + (0 if self.sender_quant else 1)
+        n = 8 + (2 if self.ns else 0) + (0 if self.sender_quant else 1)
+        if self.fused_silu:
+            n -= (1 if self.h_direct else 0) + (1 if self.ns and self.sh_direct else 0)
+        return n

@@ -38,7 +38,8 @@ def _check_tied(q: QExpertConfig):
 class MoELayer:
     def __init__(self, handle: ops.Handle, E: int, topk: int, H: int, I: int, ns: int, qlayer: QLayerConfig,
                  max_tokens: int, hadamard_down: bool = False, expert_ids: Optional[Sequence[int]] = None, seed: int = 42,
-                 weights: Optional[dict] = None, device: Optional[torch.device] = None, weight_scale: float = 1.0):
+                 weights: Optional[dict] = None, device: Optional[torch.device] = None, weight_scale: float = 1.0,
+                 fuse_silu: bool = True):
         """expert_ids: the routed experts this rank owns (expert-parallel shard); default all E.
         weights: optional {expert_idx: (W_gate_up fp16 [2I',H], W_down fp16 [H,I'])}; default U(-1,1) seed 42
         (the reference bench's distribution, test.cu:877-915)."""
@@ -50,6 +51,10 @@ class MoELayer:
         self.EL = len(self.local_experts)
         self.max_tokens = max_tokens
         self.experts: List[ExpertWeights] = []
+        ids_all = self.local_experts + ([E] if ns else [])
+        # Fuse act_fn(gate)*up into the gate_up GEMM epilogue (MXB_EPI_SILU_MUL) when every problem of the launch is
+        # one the CTA-pair kernel covers; otherwise the two-step path (GroupGEMM -> mxb_silu_mul_quant) runs.
+        self.fused_silu = fuse_silu and all(self._pair_ok(qlayer.experts[str(e)].gate) for e in ids_all)
         gen = torch.Generator(device=self.dev).manual_seed(seed)
         ids = self.local_experts + ([E] if ns else [])
         for e in ids:
@@ -62,12 +67,22 @@ class MoELayer:
             else:
                 Wgu = torch.rand(2 * Ie, H, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).mul_(weight_scale).half()
                 Wdn = torch.rand(H, Ie, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).mul_(weight_scale).half()
-            self.experts.append(ExpertWeights(*self._pack(Wgu, qe.gate), *self._pack(Wdn, qe.down), qe.gate, qe.down))
+            gu_p, gu_s = self._pack(Wgu, qe.gate)
+            if self.fused_silu:  # rows (gate_i, up_i) adjacent: the epilogue pairs neighbouring TMEM lanes
+                gu_p = handle.interleave_gate_up(gu_p)
+                gu_s = handle.interleave_gate_up(gu_s) if gu_s is not None else None
+            self.experts.append(ExpertWeights(gu_p, gu_s, *self._pack(Wdn, qe.down), qe.gate, qe.down))
             del Wgu, Wdn
         self._alloc(max_tokens)
         self._build_problems()
 
     # ------------------------------------------------------------------ setup
+    @staticmethod
+    def _pair_ok(q: QLinearConfig) -> bool:
+        if q.w_bits == 16 and q.a_bits == 16:
+            return True
+        return q.w_bits == q.a_bits and q.w_bits in (4, 8) and q.w_gsize == -1 and q.w_sym
+
     def _pack(self, W: torch.Tensor, q: QLinearConfig):
         if q.w_bits == 16:
             return W.contiguous(), None
@@ -80,14 +95,18 @@ class MoELayer:
         qs = [e.q_gu for e in self.experts[:self.EL]] + [e.q_dn for e in self.experts[:self.EL]]
         any_q = any(q.a_bits < 16 for q in qs)
         any_f = any(q.a_bits >= 16 for q in qs)
+        any_q_dn = any(e.q_dn.a_bits < 16 for e in self.experts[:self.EL])
         g_gu = any(q.a_bits < 16 and q.a_gsize == 128 for q in [e.q_gu for e in self.experts[:self.EL]])
         g_dn = any(q.a_bits < 16 and q.a_gsize == 128 for q in [e.q_dn for e in self.experts[:self.EL]])
         self.x_q8 = torch.empty(R, H, dtype=i8, device=d) if any_q else None
         self.x_f16 = torch.empty(R, H, dtype=f16, device=d) if any_f else None
         self.x_sc = torch.empty(R, H // 128 if g_gu else 1, dtype=f16, device=d) if any_q else None
-        self.gu_out = torch.empty(R, 2 * I, dtype=f16, device=d)
+        # gate_up output: [R, 2I] (two-step) or already silu(gate)*up [R, I] (fused epilogue)
+        self.gu_out = torch.empty(R, I if self.fused_silu else 2 * I, dtype=f16, device=d)
+        # fp16-only down experts without a rotation consume the fused output directly
+        self.h_direct = self.fused_silu and not any_q_dn and not self.hadamard_down
         self.h_q8 = torch.empty(R, I, dtype=i8, device=d) if any_q else None
-        self.h_f16 = torch.empty(R, I, dtype=f16, device=d) if any_f else None
+        self.h_f16 = (self.gu_out if self.h_direct else torch.empty(R, I, dtype=f16, device=d)) if any_f else None
         self.h_sc = torch.empty(R, I // 128 if g_dn else 1, dtype=f16, device=d) if any_q else None
         self.dn_out = torch.empty(R, H, dtype=f16, device=d)
         if self.ns:
@@ -95,18 +114,19 @@ class MoELayer:
             Is = I * self.ns
             self.sx_q8 = torch.empty(T, H, dtype=i8, device=d) if s.q_gu.a_bits < 16 else None
             self.sx_sc = torch.empty(T, H // 128 if s.q_gu.a_gsize == 128 else 1, dtype=f16, device=d) if s.q_gu.a_bits < 16 else None
-            self.s_gu = torch.empty(T, 2 * Is, dtype=f16, device=d)
+            self.s_gu = torch.empty(T, Is if self.fused_silu else 2 * Is, dtype=f16, device=d)
+            self.sh_direct = self.fused_silu and s.q_dn.a_bits >= 16 and not self.hadamard_down
             # like the reference workload (gen_workload.py:101) the shared down problem takes the gate config
             self.sh_q8 = torch.empty(T, Is, dtype=i8, device=d) if s.q_dn.a_bits < 16 else None
-            self.sh_f16 = torch.empty(T, Is, dtype=f16, device=d) if s.q_dn.a_bits >= 16 else None
+            self.sh_f16 = (self.s_gu if self.sh_direct else torch.empty(T, Is, dtype=f16, device=d)) if s.q_dn.a_bits >= 16 else None
             self.sh_sc = torch.empty(T, Is // 128 if s.q_dn.a_gsize == 128 else 1, dtype=f16, device=d) if s.q_dn.a_bits < 16 else None
             self.s_dn = torch.empty(T, H, dtype=f16, device=d)
         self.offs = torch.zeros(self.EL + 1, dtype=torch.int32, device=d)
 
-    def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range):
+    def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range, flags=0):
         A = A_f16 if q.a_bits >= 16 else A_q8
         return ops.Problem(A, B, C, rows, N, K, q.w_bits, q.a_bits, q.w_gsize, q.w_sym if q.w_bits < 16 else True,
-                           scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range)
+                           scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range, flags=flags)
 
     def _build_problems(self):
         """Marshal the two problem lists once; M of every routed expert is read on the device from self.offs."""
@@ -115,7 +135,8 @@ class MoELayer:
         gu, dn = [], []
         for i, ew in enumerate(self.experts[:self.EL]):
             mr = self.offs[i:i + 2]
-            gu.append(self._problem(ew.q_gu, self.x_q8, self.x_f16, self.x_sc, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * I, H, mr))
+            gu.append(self._problem(ew.q_gu, self.x_q8, self.x_f16, self.x_sc, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * I, H, mr,
+                                    flags=ops.EPI_SILU_MUL if self.fused_silu else 0))
             dn.append(self._problem(ew.q_dn, self.h_q8, self.h_f16, self.h_sc, ew.dn_packed, ew.dn_scale, self.dn_out, R, H, I, mr))
         self._gu_routed, self._dn_routed = gu, dn
         self._T_built = None
@@ -128,7 +149,8 @@ class MoELayer:
             s = self.experts[-1]
             Is = self.I * self.ns
             A_f16 = x if s.q_gu.a_bits >= 16 else None
-            gu.append(self._problem(s.q_gu, self.sx_q8, A_f16, self.sx_sc, s.gu_packed, s.gu_scale, self.s_gu, T, 2 * Is, self.H, None))
+            gu.append(self._problem(s.q_gu, self.sx_q8, A_f16, self.sx_sc, s.gu_packed, s.gu_scale, self.s_gu, T, 2 * Is, self.H, None,
+                                    flags=ops.EPI_SILU_MUL if self.fused_silu else 0))
             dn.append(self._problem(s.q_dn, self.sh_q8, self.sh_f16, self.sh_sc, s.dn_packed, s.dn_scale, self.s_dn, T, self.H, Is, None))
         self._gu_arr = self.h.pack_problems(gu)
         self._dn_arr = self.h.pack_problems(dn)
@@ -165,11 +187,20 @@ class MoELayer:
             if s.q_gu.a_bits < 16:
                 h.quant_act(x, None, T_shared, None, [(s.q_gu.a_bits, s.q_gu.a_gsize)], False, self.sx_q8, None, self.sx_sc)
         h.group_gemm(self._gu_arr)
-        h.silu_mul_quant(self.gu_out, n_rows, self.offs, self.actq_dn(), self.hadamard_down, self.h_q8, self.h_f16, self.h_sc)
-        if self.ns:
-            s = self.experts[-1]
-            h.silu_mul_quant(self.s_gu, T_shared, None, [(s.q_dn.a_bits, s.q_dn.a_gsize)], self.hadamard_down, self.sh_q8,
-                             self.sh_f16, self.sh_sc)
+        if self.fused_silu:
+            # the GEMM epilogue already produced silu(gate)*up: (rotate +) quantize it for the down GEMM
+            if not self.h_direct:
+                h.quant_act(self.gu_out, None, n_rows, self.offs, self.actq_dn(), self.hadamard_down, self.h_q8, self.h_f16, self.h_sc)
+            if self.ns and not self.sh_direct:
+                s = self.experts[-1]
+                h.quant_act(self.s_gu, None, T_shared, None, [(s.q_dn.a_bits, s.q_dn.a_gsize)], self.hadamard_down, self.sh_q8,
+                            self.sh_f16, self.sh_sc)
+        else:
+            h.silu_mul_quant(self.gu_out, n_rows, self.offs, self.actq_dn(), self.hadamard_down, self.h_q8, self.h_f16, self.h_sc)
+            if self.ns:
+                s = self.experts[-1]
+                h.silu_mul_quant(self.s_gu, T_shared, None, [(s.q_dn.a_bits, s.q_dn.a_gsize)], self.hadamard_down, self.sh_q8,
+                                 self.sh_f16, self.sh_sc)
         h.group_gemm(self._dn_arr)
 
     def gemm_ops(self, counts: Sequence[int], T_shared: int) -> int:
@@ -194,7 +225,10 @@ class MoELayer:
 
     def launches_per_step(self) -> int:
         # permute (2) + act-quant (1 [+1 shared]) + GroupGEMM (1) + silu*mul+quant (1 [+1 shared]) + GroupGEMM (1) + combine (1)
-        return 7 + (2 if self.ns else 0)
+        n = 7 + (2 if self.ns else 0)
+        if self.fused_silu:
+            n -= (1 if self.h_direct else 0) + (1 if self.ns and self.sh_direct else 0)
+        return n
 
     def weight_bytes(self, active=None) -> int:
         """bytes of packed weights + scales; `active[i]` masks routed local experts (the shared expert always counts)"""

@@ -21,6 +21,9 @@ import torch
 _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmxmoe_b200.so")
 
 
+EPI_SILU_MUL = 1  # MXB_EPI_SILU_MUL
+
+
 class MxbError(RuntimeError):
     pass
 
@@ -32,7 +35,7 @@ class MxbProblem(C.Structure):
         ("lda", C.c_int64), ("ldc", C.c_int64),
         ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
         ("a_bits", C.c_int32), ("w_bits", C.c_int32), ("gsize", C.c_int32), ("sym", C.c_int32),
-        ("tile_n", C.c_int32), ("reserved", C.c_int32),
+        ("tile_n", C.c_int32), ("flags", C.c_int32),
     ]
 
 
@@ -63,6 +66,7 @@ EXPORTS = [
     ("mxb_combine", _I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _P]),
     ("mxb_quant_pack_weight", _I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     ("mxb_repack_from_ref", _I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    ("mxb_interleave_gate_up", _I, [_P, _P, _I, _I64, _P, _P]),
     ("mxb_packed_bytes", _I64, [_I, _I, _I]),
     ("mxb_scale_elems", _I64, [_I, _I, _I, _I, _I, _I]),
     ("mxb_select_tiles", _I, [_P, C.POINTER(MxbProblem), _I, C.POINTER(MxbTileChoice)]),
@@ -115,11 +119,12 @@ class Problem:
     lda: int = 0
     ldc: int = 0
     tile_n: int = 0
+    flags: int = 0  # EPI_SILU_MUL: B rows interleaved (gate_i, up_i), C = silu(gate)*up [M, N/2]
 
     def to_c(self) -> MxbProblem:
         return MxbProblem(_ptr(self.A), _ptr(self.B), _ptr(self.scale_a), _ptr(self.scale_b), _ptr(self.C),
                           _ptr(self.m_range), self.lda, self.ldc, self.M, self.N, self.K, self.a_bits, self.w_bits,
-                          self.gsize, 1 if self.sym else 0, self.tile_n, 0)
+                          self.gsize, 1 if self.sym else 0, self.tile_n, self.flags)
 
 
 class Handle:
@@ -175,6 +180,19 @@ class Handle:
             ptrs = (C.c_void_p * n)(*[_ptr(t) for t in acc_out])
             rc = self.lib.mxb_group_gemm_debug_acc(self.h, arr, n, ptrs, _stream())
         self._check(rc, "mxb_group_gemm")
+
+    def interleave_gate_up(self, t: torch.Tensor) -> torch.Tensor:
+        """[gate rows; up rows] -> rows (gate_0, up_0, gate_1, up_1, ...) of a packed weight matrix or a scale vector."""
+        t = t.contiguous()
+        rows = t.shape[0]
+        if t.dim() == 2 and rows == 1:  # per-channel scales in the group-major [1, N(,2)] layout of permute_scale
+            rows = t.shape[1]
+        assert rows % 2 == 0
+        row_bytes = t.numel() * t.element_size() // rows
+        out = torch.empty_like(t)
+        self._check(self.lib.mxb_interleave_gate_up(self.h, _ptr(t), rows // 2, row_bytes, _ptr(out), _stream()),
+                    "mxb_interleave_gate_up")
+        return out
 
     def select_tiles(self, problems: Sequence[Problem]) -> List[MxbTileChoice]:
         arr = self.pack_problems(problems)

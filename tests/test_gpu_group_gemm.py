@@ -343,3 +343,35 @@ def test_pair_kernel_rejects_ineligible_list(HP):
     p, _, _ = make_problem(ops, rng, 64, 128, 256, 4, 4, 128, True)
     with pytest.raises(ops.MxbError, match="CTA pairs"):
         HP.group_gemm([p])
+
+
+@pytest.mark.parametrize("w_bits", [16, 8, 4])
+@pytest.mark.parametrize("M", [1, 31, 200, 546])
+def test_pair_kernel_fused_silu_mul_is_bit_identical_to_two_steps(HP, w_bits, M):
+    """MXB_EPI_SILU_MUL (gate_up GEMM writes silu(gate)*up over interleaved weight rows) must equal, bit for bit,
+    the reference's two-step pipeline: GroupGEMM -> fp16 [M,2I] -> silu_mul (ref_bind.cu:595-757) in fp16 mode; and
+    the two-step result is itself checked against the oracle."""
+    from mxmoe_b200 import ops
+    rng = np.random.default_rng(w_bits * 31 + M)
+    I, K = 192, 640
+    p, ref, _ = make_problem(ops, rng, M, 2 * I, K, w_bits, w_bits, -1, True)
+    HP.group_gemm([p])
+    check([p], [ref], [None if w_bits == 16 else None])
+    _, two_step, _ = HP.silu_mul_quant(p.C, M, None, [(16, -1)])
+    ref_h = O.silu_mul(ref)
+    assert np.abs(two_step.cpu().numpy().astype(np.float32) - ref_h.astype(np.float32)).max() <= 2e-3 * max(1.0, np.abs(ref_h).max())
+    Cf = torch.full((M, I), float("nan"), dtype=torch.float16, device="cuda")
+    pf = ops.Problem(p.A, HP.interleave_gate_up(p.B), Cf, M, 2 * I, K, p.w_bits, p.a_bits, p.gsize, p.sym, scale_a=p.scale_a,
+                     scale_b=None if p.scale_b is None else HP.interleave_gate_up(p.scale_b), flags=ops.EPI_SILU_MUL)
+    HP.group_gemm([pf])
+    torch.cuda.synchronize()
+    assert torch.equal(Cf.view(torch.int16), two_step.view(torch.int16)), "fused silu*mul differs from the two-step path"
+
+
+def test_fused_silu_mul_needs_the_pair_kernel():
+    from mxmoe_b200 import ops
+    h = ops.Handle(0)
+    h.set_gemm_path(1)
+    t = torch.zeros(128, 128, dtype=torch.float16, device="cuda")
+    with pytest.raises(ops.MxbError, match="CTA-pair"):
+        h.group_gemm([ops.Problem(t, t, t, 128, 128, 128, flags=ops.EPI_SILU_MUL)])

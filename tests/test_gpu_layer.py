@@ -73,3 +73,32 @@ def test_layer_mixed_with_hadamard():
     scale = np.abs(r).max()
     assert np.abs(o - r).max() <= 2e-2 * scale
     assert np.mean(np.abs(o - r) > 2e-3 * scale) < 0.01
+
+
+@pytest.mark.parametrize("hadamard", [False, True])
+def test_fused_silu_epilogue_layer_is_bit_identical(hadamard):
+    """The layer with silu(gate)*up fused into the gate_up GroupGEMM epilogue (CTA-pair kernel, MXB_EPI_SILU_MUL)
+    against the same layer run as the reference's two steps (GroupGEMM -> silu_mul_then_quant): identical bits."""
+    from mxmoe_b200 import ops
+    from mxmoe_b200.config import qmodel_cfg_from_dict
+    from mxmoe_b200.layer import MoELayer
+    E, k, Hd, I, ns, T = 5, 2, 256, 1408, 1, 200
+    cfgs = [(lin(8, 8), lin(4, 4)), (lin(4, 4), lin(8, 8)), (lin(16, 16), lin(16, 16))]
+    ex = {}
+    for e in range(E + 1):
+        gu, dn = cfgs[e % len(cfgs)]
+        ex[str(e)] = {"gate": gu, "up": dict(gu), "down": dn}
+    ql = qmodel_cfg_from_dict({"0": {"experts": ex}}).layers["0"]
+    g = torch.Generator().manual_seed(3)
+    x = (torch.rand(T, Hd, generator=g) * 2 - 1).half().cuda()
+    ids = torch.stack([torch.randperm(E, generator=g)[:k] for _ in range(T)]).int().cuda()
+    w = torch.rand(T, k, generator=g).cuda()
+    h = ops.Handle(0)
+    outs = []
+    for fuse in (True, False):
+        layer = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, hadamard_down=hadamard, weight_scale=0.05, fuse_silu=fuse)
+        assert layer.fused_silu == fuse
+        outs.append(layer.forward(x, ids, w).clone())
+    torch.cuda.synchronize()
+    assert torch.isfinite(outs[0].float()).all()
+    assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))
