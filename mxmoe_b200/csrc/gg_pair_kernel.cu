@@ -36,6 +36,7 @@ using namespace ptx;
 namespace {
 
 constexpr int GP_STAGES = 6;
+constexpr int GP_THREADS = 512;  // 16 warps: TMA tokens, MMA, TMEM alloc, TMA weights, 4 epilogue, 4 converter, 4 epilogue
 constexpr int GP_W_BYTES = 128 * 128;  // this CTA's 128 weight rows x 128 B
 constexpr int GP_T_BYTES = 128 * 128;  // this CTA's half of the token tile, <= 128 rows x 128 B
 constexpr int GP_STAGE_BYTES = GP_W_BYTES + GP_T_BYTES;
@@ -52,7 +53,7 @@ struct Smem {
   uint64_t* conv;        // [S] leader: converter warps of both CTAs finished (8 arrivals)
   uint64_t* cfull;       // [S] each CTA: its own packed weights landed
   uint64_t* tmem_full;   // [2] each CTA (multicast commit)
-  uint64_t* tmem_empty;  // [2] leader: epilogue warps of both CTAs drained the accumulator (8 arrivals)
+  uint64_t* tmem_empty;  // [2] leader: epilogue warps of both CTAs drained the accumulator (16 arrivals)
   uint32_t* tmem_ptr;
   __half* sa_stage;      // [2][256] per-token scales of the tile being drained
   int32_t* prefix;       // [P+1]
@@ -121,7 +122,7 @@ __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
 
 }  // namespace
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pair_kernel(const DevProblem* __restrict__ probs, int P) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pair_kernel(const DevProblem* __restrict__ probs, int P) {
   extern __shared__ uint8_t smem_raw[];
   Smem S = carve(smem_raw);
   const int warp = threadIdx.x >> 5;
@@ -130,7 +131,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
   const bool leader = rank == 0;
 
   // ---- device-side tile table (M may live in device memory: DevProblem::m_range)
-  for (int p = threadIdx.x; p < P; p += GG_THREADS) {
+  for (int p = threadIdx.x; p < P; p += GP_THREADS) {
     const DevProblem& d = probs[p];
     int m = d.M, r0 = 0;
     if (d.m_range != nullptr) {
@@ -151,7 +152,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&S.tmem_full[i], 1);
-      mbar_init(&S.tmem_empty[i], 8);
+      mbar_init(&S.tmem_empty[i], 16);
     }
     fence_mbar_init();
   }
@@ -274,10 +275,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
-  } else if (warp >= 4 && warp < 8) {
-    // ============================================================ epilogue (4 warps in EACH CTA; lane = weight row)
-    const int q = warp - 4;
-    const int et = threadIdx.x - 128;  // 0..127
+  } else if ((warp >= 4 && warp < 8) || warp >= 12) {
+    // ============================================================ epilogue (8 warps in EACH CTA; lane = weight row)
+    // Two warps per TMEM lane quadrant (warps q+4 and q+12, both on scheduler q), taking alternate
+    // 32-token column chunks: one warp per scheduler could not hide the latency of its own dependent chains.
+    const int q = warp & 3;
+    const int grp = warp >= 12 ? 1 : 0;
+    const int et = grp * 128 + q * 32 + lane;  // 0..255
     int acc = 0;
     uint32_t acc_phase = 0;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
@@ -298,21 +302,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
       if (epi == EPI_INT_ROWCOL) {
         // stage the tile's per-token scales (each thread 2 of them), fetch this lane's per-channel scale
         const __half* sa = d.scale_a + grow0;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int c = et + i * 128;
-          sa_buf[c] = c < t.nt ? sa[c] : __float2half(0.f);
-        }
+        sa_buf[et] = et < t.nt ? sa[et] : __float2half(0.f);
         if (n_ok) sb2 = __half2half2(d.scale_b[n]);
       }
-      // every tile, also the unscaled ones: keeps the four warps within one tile of each other, which is what makes
+      // every tile, also the unscaled ones: keeps the eight warps within one tile of each other, which is what makes
       // the two-deep sa_stage buffer safe
-      named_bar_sync(2, 128);
+      named_bar_sync(2, 256);
       __half* Cp = d.C + static_cast<int64_t>(grow0) * ldc + n;
       int32_t* ao = d.acc_out != nullptr ? d.acc_out + static_cast<int64_t>(t.t0) * N + n : nullptr;
       mbar_wait(&S.tmem_full[acc], acc_phase);
       tc_fence_after();
-      for (int c = 0; c < t.nt; c += 32) {
+      for (int c = grp * 32; c < t.nt; c += 64) {
         uint32_t v[32];
         tmem_ld_32x32(lane_addr + acc * 256 + c, v);
         tmem_ld_wait();
@@ -386,7 +386,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GG_THREADS, 1) gg_pa
       if (lane == 0) mbar_arrive_cluster(tmem_empty_leader + acc * 8);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-  } else if (warp >= 8) {
+  } else if (warp >= 8 && warp < 12) {
     // ============================================================ 4-bit weight converters (4 warps in EACH CTA)
     const int ct = threadIdx.x - 256;  // 0..127
     int stage = 0;
@@ -450,7 +450,7 @@ int gg_pair_smem_bytes() { return GP_SMEM_BYTES; }
 int gg_pair_stages() { return GP_STAGES; }
 
 void gg_pair_launch(const DevProblem* probs, int P, int grid, cudaStream_t stream) {
-  gg_pair_kernel<<<grid & ~1, GG_THREADS, GP_SMEM_BYTES, stream>>>(probs, P);
+  gg_pair_kernel<<<grid & ~1, GP_THREADS, GP_SMEM_BYTES, stream>>>(probs, P);
 }
 
 }  // namespace mxb
