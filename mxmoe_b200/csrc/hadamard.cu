@@ -17,6 +17,7 @@
 #include <stdlib.h>
 
 #include "moe_ops.cuh"
+#include "ptx.cuh"
 #include "quant_common.cuh"
 
 namespace mxb {
@@ -201,6 +202,7 @@ __global__ void __launch_bounds__(256) hadamard_quant_kernel(HadParams p) {
 
 
 #include "hadamard_mma.inc"
+#include "hadamard_umma.inc"
 
 }  // namespace
 
@@ -241,6 +243,14 @@ cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t
   p.scale = static_cast<float>(1.0 / sqrt(static_cast<double>(n)));
   p.h_pitch = Kp * 2 + 16;
   { const char* e = getenv("MXB_HAD_DBG"); p.dbg = e ? atoi(e) : 0; }
+  static const int use_umma = [] { const char* e = getenv("MXB_HAD_UMMA"); return e ? atoi(e) : 1; }();
+  if (use_umma && K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {  // tcgen05 form (hadamard_umma.inc)
+    if (Kp == 176) return launch_umma<11>(silu, p, sm_count, st);
+    if (Kp == 48) return launch_umma<3>(silu, p, sm_count, st);
+    if (Kp == 32) return launch_umma<2>(silu, p, sm_count, st);
+    if (Kp == 16) return launch_umma<1>(silu, p, sm_count, st);
+    if (Kp == 64) return launch_umma<4>(silu, p, sm_count, st);
+  }
   if (K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {
     if (Kp == 176) return launch_mma<11>(silu, p, sm_count, st);
     if (Kp == 48) return launch_mma<3>(silu, p, sm_count, st);

@@ -123,6 +123,19 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   return d;
 }
 
+// MN-major operand (element (mn, k) with mn contiguous) in the canonical 128-byte-swizzle layout: atoms of
+// 64 mn x 8 k (8 rows of 128 B, 16-byte chunk index XOR k%8); SBO = bytes between 8-k groups, LBO = bytes between
+// 64-mn blocks (cute: Swizzle<3,4,3> o ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes = 1024) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+
 // Instruction descriptor (upper 32 bits of the "idesc" operand), both operands K-major, dense.
 //   c_format [4,6): 1 = f32, 2 = s32;  a_format [7,10), b_format [10,13);  N>>3 at [17,23);  M>>4 at [24,29)
 enum : uint32_t { UMMA_FMT_F16 = 0, UMMA_FMT_BF16 = 1, UMMA_FMT_S8 = 1, UMMA_FMT_E4M3 = 0 };
