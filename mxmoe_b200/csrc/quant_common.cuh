@@ -62,16 +62,23 @@ __device__ __forceinline__ int find_expert(const int32_t* __restrict__ offs, int
 // x and s are fp16 values, so x/s is either exactly representable in fp32 or at least one fp32 ulp away from every
 // fp16 rounding boundary: half(q1) == half(x/s) always (and the GPU tests compare bit-for-bit with the oracle).
 __device__ __forceinline__ uint2 quant8(const float (&v)[8], float sf, float rcp, int upper) {
-  uint2 pk;
-  int8_t* pb = reinterpret_cast<int8_t*>(&pk);
+  // The tail runs on packed halves and never touches the conversion (XU) pipe: the two quotients are rounded to fp16
+  // together (one F2FP), clamped with HMNMX2, and rounded to integers (ties to even, torch.round) by adding 1536 in
+  // fp16 — in [1024, 2048) the fp16 spacing is 1, so the low byte of the sum's bit pattern is the two's-complement code.
+  const __half2 hi2 = __float2half2_rn(static_cast<float>(upper)), lo2 = __float2half2_rn(static_cast<float>(-upper));
+  const __half2 magic = __float2half2_rn(1536.f);
+  uint32_t w[4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float q0 = v[j] * rcp;
-    const float q1 = fmaf(fmaf(-q0, sf, v[j]), rcp, q0);
-    int qi = __float2int_rn(h_round(q1));
-    qi = max(-upper, min(upper, qi));
-    pb[j] = static_cast<int8_t>(qi);
+  for (int j = 0; j < 4; ++j) {
+    const float a0 = v[2 * j] * rcp, b0 = v[2 * j + 1] * rcp;
+    const float a1 = fmaf(fmaf(-a0, sf, v[2 * j]), rcp, a0), b1 = fmaf(fmaf(-b0, sf, v[2 * j + 1]), rcp, b0);
+    __half2 q = __floats2half2_rn(a1, b1);
+    q = __hadd2(__hmax2(__hmin2(q, hi2), lo2), magic);
+    w[j] = *reinterpret_cast<uint32_t*>(&q);
   }
+  uint2 pk;
+  pk.x = __byte_perm(w[0], w[1], 0x6420);
+  pk.y = __byte_perm(w[2], w[3], 0x6420);
   return pk;
 }
 __device__ __forceinline__ __half make_scale(float amax, float upper) {
