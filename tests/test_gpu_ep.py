@@ -32,7 +32,7 @@ def _worker(rank, world, port, mixed_f16, q):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        E, k, Hd, I, ns, T = 6, 2, 256, 128, 2, 200
+        E, k, Hd, I, ns, T = 6, 2, 256, 128, 2, 300  # T*k > 512 rows: both layers take the tcgen05 path for the w4a16 expert
         cfgs = [(_lin(8, 8), _lin(4, 4)), (_lin(4, 4), _lin(8, 8)), (_lin(4, 4), _lin(4, 4))]
         if mixed_f16:
             cfgs.append((_lin(16, 16), _lin(4, 16, 128, False)))
