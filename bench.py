@@ -272,19 +272,22 @@ def main():
             io_bytes += T * (s["H"] * act_bytes + 3 * s["I"] * s["ns"] * 2 + s["H"] * 2)
         ach = (w_bytes + io_bytes) * steps / (ms_gemm * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None,
-                "kernel": "gg_persistent_kernel + w4a16_stream_kernel (gate_up + down launches of one step)",
+                "kernel": ("gg_pair_kernel" if layer.fused_silu else "gg_persistent_kernel + w4a16_stream_kernel") + " (gate_up + down launches of one step)",
                 "peak_source": pk["src"] + " copy bandwidth",
                 "algorithmic": f"{w_bytes} B packed weights of the active experts + {io_bytes} B activations in/out per step",
                 "ms_per_launch_pair": ms_gemm / steps}
     else:
         ach = my_gemm_ops * steps / (ms_gemm * 1e-3) / 1e12
         # dram__bytes_read.sum + dram__bytes_write.sum of the two launches from one `ncu --set full` capture of this command
-        # (profiles/ncu_gg_persistent_r01.txt); only known for the default workload on one GPU
-        traffic = 978.4e6 if (args.workload == "c2" and W == 1 and not args.bs) else None
+        # (profiles/ncu_gg_pair_r01.txt: 315.2 + 138.3 MB gate_up, 212.9 + 148.8 MB down); only known for the default
+        # workload on one GPU
+        traffic = 815.2e6 if (args.workload == "c2" and W == 1 and not args.bs) else None
         roof = {"bound": "tensor", "achieved": ach, "peak": int8_peak, "unit": "TOPS", "frac": ach / int8_peak, "traffic": traffic,
-                "kernel": "gg_persistent_kernel (2 launches/step: gate_up + down)",
+                "kernel": "gg_pair_kernel (2 launches/step: gate_up with fused silu*mul epilogue + down)" if layer.fused_silu
+                else "gg_persistent_kernel (2 launches/step: gate_up + down)",
                 "peak_source": f"2 x {pk['src']} cuBLAS bf16 burst ({pk['bf16']} TFLOPS): int8 dense = 2x bf16 on sm_100",
-                "algorithmic": "sum 2*M*N*K of the launch's problems", "ms_per_launch_pair": ms_gemm / steps}
+                "algorithmic": "sum 2*M*N*K of the launch's problems", "ms_per_launch_pair": ms_gemm / steps,
+                "mma_issue_peak": "tools/mma_peak.cu on this pool: 4590 TOPS kind::i8, 2232 TFLOPS kind::f16 with operands resident in smem"}
 
     line = {"metric": "MoE-layer GroupGEMM TOPS", "value": value, "unit": "TOPS", "n_gpus": W, "steps": steps, "warmup": warmup,
             "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -93,7 +93,8 @@ typedef struct MxbActQ {
 
 typedef struct MxbTileChoice {
   int32_t tile_m, tile_n, tile_k, stages;
-  int32_t path;       /* 0 = tcgen05 persistent GroupGEMM, 1 = HBM-streaming w4a16 */
+  int32_t path;       /* 0 = single-CTA tcgen05 GroupGEMM, 1 = HBM-streaming w4a16, 2 = CTA-pair tcgen05 GroupGEMM
+                         (tile_m = weight rows, tile_n = tokens per tile) */
   float est_us;       /* cost-model estimate for this problem alone */
 } MxbTileChoice;
 

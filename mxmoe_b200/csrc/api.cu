@@ -219,7 +219,8 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   // tile_config.py:330-610): 4-bit weight-only problems with at most 16 rows stream through w4a16_stream.cu.
   // With device-resident M the row capacity of the shared buffer decides (decode batches).
   const int m_cap = p.m_range ? (p.M <= 512 ? 16 : p.M) : p.M;
-  d->path = (!paired && k.conv == mxb::CONV_W4_F16 && m_cap <= 16 && p.K % 128 == 0 && p.tile_n == 0) ? 1 : 0;
+  d->path = (!paired && k.conv == mxb::CONV_W4_F16 && m_cap <= 16 && p.K % 128 == 0 && p.N % 16 == 0 && p.K <= mxb::w4a16_stream_max_k() &&
+             p.tile_n == 0) ? 1 : 0;
   if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k
   else if (k.conv >= mxb::CONV_W4_F16) d->kb_per_group = p.gsize == 128 ? 2 : d->kblocks;  // fp16 slabs hold 64 k
   else d->kb_per_group = d->kblocks;
@@ -242,6 +243,10 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   const int wbox = paired ? 128 : bn;  // weight rows per TMA box (pair kernel: each CTA stages 128 of the tile's 256)
   if (k.conv == mxb::CONV_NONE) {
     rc = encode_2d(c, &d->tmB, adt, k.a_elsize, p.B, p.K, p.N, uint64_t(p.K) * k.a_elsize, k.k_per_block, wbox, true);
+  } else if (d->path == 1) {
+    // streaming kernel (w4a16_stream.cu): 16-row slabs, 128 bytes (256 k) per row and stage, 128-byte swizzle
+    const uint64_t row_bytes = uint64_t(p.K) / 2;
+    rc = encode_2d(c, &d->tmB, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p.B, row_bytes, p.N, row_bytes, 128, 16, true);
   } else {
     const uint64_t row_bytes = uint64_t(p.K) * p.w_bits / 8;
     rc = encode_2d(c, &d->tmB, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, p.B, row_bytes, p.N, row_bytes, k.b_bytes_per_kb, wbox, false);
@@ -314,7 +319,7 @@ int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* 
   const int rows_per_task = mxb::w4a16_stream_rows_per_task();
   for (int i = 0; i < P; ++i) {
     const bool st_path = host[i].path != 0;
-    if (st_path) stream_classes |= host[i].path;
+    if (st_path && host[i].K > stream_classes) stream_classes = host[i].K;  // largest K routed to the streaming kernel
     tprefix[i + 1] = tprefix[i] + (st_path ? (host[i].N + rows_per_task - 1) / rows_per_task : 0);
     if (!st_path && host[i].n_tiles > 0 && !(problems[i].M == 0 && !problems[i].m_range)) ++tc_problems;
   }
@@ -734,29 +739,57 @@ int mxb_repack_from_ref(mxb_handle_t c, const void* ref_packed, int N, int K, in
 extern "C" int mxb_select_tiles(mxb_handle_t c, const MxbProblem* problems, int P, MxbTileChoice* out) {
   if (P < 0 || (P > 0 && (!problems || !out))) return fail(MXB_EINVAL, "bad argument");
   const double sms = c ? c->sm_count : 148;
-  const double clk = 1.5e9;                       // sustained SM clock under load (MEASURED_PEAKS.json: 1.3-1.5 GHz)
-  const double hbm = 6.5e12;                      // measured copy bandwidth, B/s
+  const double clk = 1.9e9;     // SM clock of a kernel timed alone on this pool (MEASURED_PEAKS.json: 1965 MHz max)
+  const double hbm = 6.5e12;    // measured copy bandwidth, B/s
+  const double l2 = 10.0e12;    // measured L2 -> SM operand rate of the pair kernel (ncu l1tex__m_xbar2l1tex_read_bytes)
+  const int gemm_path = c ? c->gemm_path : 0;
   for (int i = 0; i < P; ++i) {
     const MxbProblem& p = problems[i];
     KindInfo k = {};
     int rc = classify(p, &k);
     if (rc) return rc;
     MxbTileChoice t;
-    t.tile_m = 128;
-    t.tile_n = pick_tile_n(p, k);
-    t.tile_k = k.k_per_block;
-    t.stages = mxb::GG_STAGES;
-    t.path = (p.a_bits == 16 && p.w_bits == 4 && p.M <= 16 && p.K % 128 == 0) ? 1 : 0;
-    // tensor time: tiles x k-slabs x 4 MMAs x (128*N/256) cycles each (B300_MICROARCH "tcgen05 floor"), spread over the SMs
-    const double tiles = double((p.M + 127) / 128) * double((p.N + t.tile_n - 1) / t.tile_n);
-    const double kb = double((p.K + k.k_per_block - 1) / k.k_per_block);
-    double cyc = tiles * kb * 4.0 * (128.0 * t.tile_n / 256.0);
-    if (k.epi == mxb::EPI_INT_GROUP) cyc *= 2.0;  // epilogue-paced: one TMEM drain per 128-K group
-    const double t_tensor = cyc / (sms * clk);
-    const double bytes = double(p.N) * p.K * p.w_bits / 8.0 + double(p.M) * p.K * (p.a_bits >= 8 ? (p.a_bits == 16 ? 2 : 1) : 1) +
-                         double(p.M) * p.N * 2.0;
-    const double t_mem = bytes / hbm;
-    t.est_us = float(1e6 * (t_tensor > t_mem ? t_tensor : t_mem));
+    const bool stream = p.a_bits == 16 && p.w_bits == 4 && p.M <= 16 && p.K % 128 == 0 && p.N % 16 == 0 &&
+                        p.K <= mxb::w4a16_stream_max_k() && p.tile_n == 0;
+    const bool pair = gemm_path != 1 && pair_eligible(p);
+    const double w_bytes = double(p.N) * p.K * p.w_bits / 8.0;
+    const double a_el = p.a_bits == 16 ? 2.0 : 1.0;
+    double t_tensor, t_l2;
+    if (pair) {
+      // CTA pair: 256 weight rows x nt tokens per tile, nt = M / ceil(M/256) rounded up to 16 (gg_pair_kernel.cu PairWalk)
+      const int tch = (p.M + 255) / 256 > 0 ? (p.M + 255) / 256 : 1;
+      const int nt = (((p.M + tch - 1) / tch) + 15) & ~15;
+      t.tile_m = 256;
+      t.tile_n = nt;
+      t.tile_k = k.k_per_block;
+      t.stages = mxb::gg_pair_stages();
+      t.path = 2;
+      const double tiles = double(tch) * double((p.N + 255) / 256);
+      const double kb = double((p.K + k.k_per_block - 1) / k.k_per_block);
+      // UMMA 256 x nt x 32 B on two SMs: nt/2 cycles per instruction, 4 instructions per 128-byte slab
+      t_tensor = tiles * kb * 4.0 * (nt / 2.0) / ((sms / 2.0) * clk);
+      // per slab and pair: 256 weight rows (128 B, or 64 B packed) + nt token rows of 128 B cross the L2 -> SM fabric
+      t_l2 = tiles * kb * (256.0 * (p.w_bits == 4 && p.a_bits == 4 ? 64.0 : 128.0) + nt * 128.0) / l2;
+    } else {
+      t.tile_m = 128;
+      t.tile_n = pick_tile_n(p, k);
+      t.tile_k = k.k_per_block;
+      t.stages = mxb::GG_STAGES;
+      t.path = stream ? 1 : 0;
+      const double tiles = double((p.M + 127) / 128) * double((p.N + t.tile_n - 1) / t.tile_n);
+      const double kb = double((p.K + k.k_per_block - 1) / k.k_per_block);
+      double cyc = tiles * kb * 4.0 * (128.0 * t.tile_n / 256.0);
+      if (k.epi == mxb::EPI_INT_GROUP) cyc *= 2.0;  // epilogue-paced: one TMEM drain per 128-K group
+      t_tensor = cyc / (sms * clk);
+      t_l2 = tiles * kb * (128.0 * 128.0 + t.tile_n * double(k.b_bytes_per_kb)) / l2;
+      if (stream) t_tensor = t_l2 = 0.0;
+    }
+    const double bytes = w_bytes + double(p.M) * p.K * a_el + double(p.M) * p.N * 2.0;
+    double t_mem = bytes / hbm;
+    if (stream) t_mem = w_bytes / 1.7e12;  // the streaming kernel is instruction-bound at ~1.7 TB/s (profiles/)
+    double tt = t_tensor > t_mem ? t_tensor : t_mem;
+    if (t_l2 > tt) tt = t_l2;
+    t.est_us = float(1e6 * tt);
     out[i] = t;
   }
   return MXB_OK;

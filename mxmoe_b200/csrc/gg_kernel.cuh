@@ -70,8 +70,9 @@ constexpr int GG_SMEM_BYTES = 1024 /*align slack*/ + GG_STAGES * GG_STAGE_BYTES 
                               (3 * GG_MAXP + 4) * 4;
 
 void gg_launch(const DevProblem* probs, int P, int grid, cudaStream_t stream);
-void w4a16_stream_launch(const DevProblem* probs, int P, const int32_t* task_prefix_dev, int total_tasks, int classes, cudaStream_t st);
+void w4a16_stream_launch(const DevProblem* probs, int P, const int32_t* task_prefix_dev, int total_tasks, int max_k, cudaStream_t st);
 int w4a16_stream_rows_per_task();
+int w4a16_stream_max_k();
 int gg_configure();  // cudaFuncSetAttribute(max dynamic smem); returns cudaError_t as int
 
 // CTA-pair kernel (gg_pair_kernel.cu): tcgen05 cta_group::2, weights as the UMMA M operand, tokens as UMMA N.

@@ -375,3 +375,59 @@ def test_fused_silu_mul_needs_the_pair_kernel():
     t = torch.zeros(128, 128, dtype=torch.float16, device="cuda")
     with pytest.raises(ops.MxbError, match="CTA-pair"):
         h.group_gemm([ops.Problem(t, t, t, 128, 128, 128, flags=ops.EPI_SILU_MUL)])
+
+
+@pytest.mark.parametrize("gsize,sym", [(128, False), (128, True), (-1, True), (-1, False)])
+@pytest.mark.parametrize("M,N,K", [(1, 16, 128), (6, 2816, 2048), (8, 528, 1408), (9, 512, 1408), (16, 2048, 1408), (3, 1040, 3584)])
+def test_w4a16_streaming_kernel(H, gsize, sym, M, N, K):
+    """HBM-streaming weight-only kernel (problems with at most 16 rows): bulk-copied weight slabs, weights on the
+    m16 side of mma.sync, every ring/tail case (K = 1408 = 2.75 stages, N not a multiple of 512, 1..16 tokens)."""
+    from mxmoe_b200 import ops
+    rng = np.random.default_rng(M * 13 + N + K + (gsize & 7) + 2 * sym)
+    p, ref, _ = make_problem(ops, rng, M, N, K, 4, 16, gsize, sym)
+    H.group_gemm([p])
+    check([p], [ref], [None])
+
+
+def test_w4a16_streaming_many_experts_device_m(H):
+    """Decode-shaped list: 40 experts sharing one activation buffer with DEVICE-resident row ranges (0..16 rows each,
+    several empty) -> one streaming launch; every expert against the oracle."""
+    from mxmoe_b200 import ops
+    rng = np.random.default_rng(77)
+    E, N, K = 40, 704, 1024
+    Ms = [int(v) for v in rng.integers(0, 17, E)]
+    Ms[3] = Ms[17] = 0
+    offs = np.concatenate([[0], np.cumsum(Ms)]).astype(np.int32)
+    tot = int(offs[-1])
+    A = rand16(rng, tot, K)
+    d_A, d_offs = dev(A), dev(offs)
+    Cb = torch.full((tot, N), float("nan"), dtype=torch.float16, device="cuda")
+    ps, refs, keep = [], [], []
+    for e in range(E):
+        W = rand16(rng, N, K)
+        q, s, z = O.quant_weight(W, 4, 128, False)
+        dB, dsc = dev(O.pack_weightonly_native(q, 4, False)), dev(O.permute_scale(s, z, False))
+        keep += [dB, dsc]
+        ps.append(ops.Problem(d_A, dB, Cb, 256, N, K, 4, 16, 128, False, scale_b=dsc, m_range=d_offs[e:e + 2]))
+        refs.append(O.gemm_wonly(A[offs[e]:offs[e + 1]], q, s, z, 128, False) if Ms[e] else None)
+    H.group_gemm(ps)
+    torch.cuda.synchronize()
+    out = Cb.cpu().numpy()
+    for e in range(E):
+        if Ms[e]:
+            assert relerr(out[offs[e]:offs[e + 1]], refs[e]) <= REL_TOL, f"expert {e}"
+
+
+def test_select_tiles_reports_the_kernel_choice(H):
+    """Blackwell tile selector (replaces tile_config.py:330-610 / bits_solver.py:425-515): path and tile per problem."""
+    from mxmoe_b200 import ops
+    t = torch.zeros(16, 16, dtype=torch.float16, device="cuda")
+    ps = [ops.Problem(t, t, t, 546, 2816, 2048, 8, 8, -1, True, scale_a=t, scale_b=t),       # CTA pair unless forced off
+          ops.Problem(t, t, t, 6, 2816, 2048, 4, 16, 128, False, scale_b=t),                 # decode: streaming kernel
+          ops.Problem(t, t, t, 546, 2816, 2048, 4, 4, 128, True, scale_a=t, scale_b=t)]      # group-wise: single-CTA kernel
+    ch = H.select_tiles(ps)
+    assert ch[1].path == 1 and ch[2].path == 0 and ch[2].tile_n == 64
+    assert ch[0].path in (0, 2)
+    if ch[0].path == 2:
+        assert (ch[0].tile_m, ch[0].tile_n) == (256, 192)  # 546 tokens -> 3 equal tiles of 182 -> 192
+    assert all(c.est_us > 0 for c in ch)
