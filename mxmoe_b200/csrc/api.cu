@@ -84,6 +84,8 @@ struct mxb_context {
   size_t ws_bytes = 0;
   int32_t* inv_tab[3] = {nullptr, nullptr, nullptr};  // repack tables for 8/4/2-bit W-only reference layout
   std::vector<std::pair<int, void*>> hads;            // device fp16 copies of the K x K Hadamard factors
+  cudaStream_t aux = nullptr;                         // fork/join side stream: tcgen05 kernel next to the streaming kernel
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 namespace {
@@ -366,8 +368,27 @@ int group_gemm_impl(mxb_context* c, const MxbProblem* problems, int P, int32_t* 
   Plan* pl = nullptr;
   int rc = get_plan(c, problems, P, acc_out, st, &pl);
   if (rc) return rc;
+  // A list that holds both decode-shaped weight-only problems (streaming kernel) and tensor-core problems (e.g. the
+  // shared expert of a decode step) runs the two kernels side by side: the persistent kernel's CTAs without tiles
+  // exit at once and the streaming CTAs take those SMs.  Fork/join with events (CUDA-graph capturable).
+  const bool both = pl->stream_tasks > 0 && pl->tc_problems > 0 && c->aux != nullptr;
+  cudaStream_t tc_st = st;
+  if (both) {
+    CU_OK(cudaEventRecord(c->ev_fork, st));
+    CU_OK(cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
+    tc_st = c->aux;
+  }
+  if (pl->tc_problems > 0 && both) {
+    for (int off = 0; off < P; off += mxb::GG_MAXP) {
+      const int n = P - off < mxb::GG_MAXP ? P - off : mxb::GG_MAXP;
+      if (pl->paired) mxb::gg_pair_launch(pl->dev + off, n, c->sm_count, tc_st);
+      else mxb::gg_launch(pl->dev + off, n, c->sm_count, tc_st);
+    }
+    CU_OK(cudaEventRecord(c->ev_join, tc_st));
+  }
   if (pl->stream_tasks > 0) mxb::w4a16_stream_launch(pl->dev, P, pl->task_prefix, pl->stream_tasks, pl->stream_classes, st);
-  if (pl->tc_problems > 0) {
+  if (both) CU_OK(cudaStreamWaitEvent(st, c->ev_join, 0));
+  if (pl->tc_problems > 0 && !both) {
     for (int off = 0; off < P; off += mxb::GG_MAXP) {
       const int n = P - off < mxb::GG_MAXP ? P - off : mxb::GG_MAXP;
       if (pl->paired) mxb::gg_pair_launch(pl->dev + off, n, c->sm_count, st);
@@ -415,6 +436,11 @@ int mxb_create(int device, mxb_handle_t* out) {
     return fail(MXB_ECUDA, "cudaFuncSetAttribute(max dynamic smem %d): %s", mxb::gg_pair_smem_bytes(), cudaGetErrorString(e));
   }
   if (const char* env = getenv("MXB_GEMM_PATH")) c->gemm_path = atoi(env);
+  if (cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    c->aux = nullptr;  // no side stream: the two kernels of a mixed list simply run back to back
+    cudaGetLastError();
+  }
   c->ws_bytes = 8u << 20;
   e = cudaMalloc(reinterpret_cast<void**>(&c->ws), c->ws_bytes);
   if (e != cudaSuccess) {
@@ -442,6 +468,9 @@ int mxb_destroy(mxb_handle_t c) {
     if (p) cudaFree(p);
   for (auto& h : c->hads) cudaFree(h.second);
   if (c->ws) cudaFree(c->ws);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->aux) cudaStreamDestroy(c->aux);
   delete c;
   return MXB_OK;
 }

@@ -192,42 +192,57 @@ namespace {
 __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__ down, int H, const int32_t* __restrict__ slot_of,
                                                        const float* __restrict__ topk_w, int T, int k,
                                                        const __half* __restrict__ shared_out, __half* __restrict__ out) {
-  const int lane = threadIdx.x & 31;
-  const int t = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (t >= T) return;
+  // one thread per (token, 8 output elements): a decode step (T of a few dozen) still spreads over the whole chip, and
+  // the k gathered rows of a thread are independent loads in flight together
   const int n8 = H >> 3;
-  for (int i = lane; i < n8; i += 32) {
-    float acc[8];
+  const int64_t id = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x;
+  if (id >= static_cast<int64_t>(T) * n8) return;
+  const int t = static_cast<int>(id / n8), i = static_cast<int>(id - static_cast<int64_t>(t) * n8);
+  float acc[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    for (int j = 0; j < k; ++j) {
-      const int slot = slot_of[t * k + j];
-      const float w = topk_w[t * k + j];
-      uint4 v = *reinterpret_cast<const uint4*>(down + static_cast<int64_t>(slot) * H + i * 8);
-      const __half* vh = reinterpret_cast<const __half*>(&v);
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int j0 = 0; j0 < k; j0 += 4) {
+    uint4 v[4];
+    float w[4];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] = fmaf(w, __half2float(vh[e]), acc[e]);
+    for (int jj = 0; jj < 4; ++jj) {
+      const int j = j0 + jj;
+      w[jj] = 0.f;
+      v[jj] = make_uint4(0, 0, 0, 0);
+      if (j < k) {
+        w[jj] = topk_w[t * k + j];
+        v[jj] = *reinterpret_cast<const uint4*>(down + static_cast<int64_t>(slot_of[t * k + j]) * H + i * 8);
+      }
     }
-    if (shared_out != nullptr) {
-      uint4 v = *reinterpret_cast<const uint4*>(shared_out + static_cast<int64_t>(t) * H + i * 8);
-      const __half* vh = reinterpret_cast<const __half*>(&v);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] = acc[e] + __half2float(vh[e]);
+    for (int jj = 0; jj < 4; ++jj) {
+      if (j0 + jj < k) {  // fp32 accumulation in j order (oracle.combine)
+        const __half* vh = reinterpret_cast<const __half*>(&v[jj]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = fmaf(w[jj], __half2float(vh[e]), acc[e]);
+      }
     }
-    uint4 pk;
-    __half2* ph = reinterpret_cast<__half2*>(&pk);
-#pragma unroll
-    for (int e = 0; e < 4; ++e) ph[e] = __floats2half2_rn(acc[2 * e], acc[2 * e + 1]);
-    *reinterpret_cast<uint4*>(out + static_cast<int64_t>(t) * H + i * 8) = pk;
   }
+  if (shared_out != nullptr) {
+    uint4 v = *reinterpret_cast<const uint4*>(shared_out + static_cast<int64_t>(t) * H + i * 8);
+    const __half* vh = reinterpret_cast<const __half*>(&v);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = acc[e] + __half2float(vh[e]);
+  }
+  uint4 pk;
+  __half2* ph = reinterpret_cast<__half2*>(&pk);
+#pragma unroll
+  for (int e = 0; e < 4; ++e) ph[e] = __floats2half2_rn(acc[2 * e], acc[2 * e + 1]);
+  *reinterpret_cast<uint4*>(out + static_cast<int64_t>(t) * H + i * 8) = pk;
 }
 }  // namespace
 
 cudaError_t combine_launch(const void* down, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
                            const void* shared_out, void* out, cudaStream_t st) {
   if (T == 0) return cudaSuccess;
-  combine_kernel<<<(T + 7) / 8, 256, 0, st>>>(static_cast<const __half*>(down), H, slot_of, topk_w, T, k,
-                                              static_cast<const __half*>(shared_out), static_cast<__half*>(out));
+  const int64_t units = static_cast<int64_t>(T) * (H >> 3);
+  combine_kernel<<<static_cast<unsigned>((units + 255) / 256), 256, 0, st>>>(static_cast<const __half*>(down), H, slot_of, topk_w, T, k,
+                                                                           static_cast<const __half*>(shared_out), static_cast<__half*>(out));
   return cudaGetLastError();
 }
 
