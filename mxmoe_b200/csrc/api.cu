@@ -56,7 +56,6 @@ struct Plan {
   uint64_t key = 0;
   int P = 0;
   mxb::DevProblem* dev = nullptr;  // device array, capacity GG_MAXP per chunk list
-  int32_t* task_prefix = nullptr;  // [P+1] slab prefix of the problems routed to the streaming kernel
   int stream_tasks = 0, tc_problems = 0, stream_classes = 0;
   bool paired = false;             // problems are encoded for gg_pair_kernel (CTA pairs, cta_group::2)
   size_t cap = 0;
@@ -220,8 +219,10 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   // Path choice (replaces the reference's per-qconfig tile lists for the memory-bound experts,
   // tile_config.py:330-610): 4-bit weight-only problems with at most 16 rows stream through w4a16_stream.cu.
   // With device-resident M the row capacity of the shared buffer decides (decode batches).
+  // Up to 64 rows (four 16-token passes over L2-resident slabs) the streaming kernel still beats a 128-row UMMA tile
+  // fed by the converter warps, and a decode step's shared expert then rides in the same launch.
   const int m_cap = p.m_range ? (p.M <= 512 ? 16 : p.M) : p.M;
-  d->path = (!paired && k.conv == mxb::CONV_W4_F16 && m_cap <= 16 && p.K % 128 == 0 && p.N % 16 == 0 && p.K <= mxb::w4a16_stream_max_k() &&
+  d->path = (!paired && k.conv == mxb::CONV_W4_F16 && m_cap <= 64 && p.K % 128 == 0 && p.N % 16 == 0 && p.K <= mxb::w4a16_stream_max_k() &&
              p.tile_n == 0) ? 1 : 0;
   if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k
   else if (k.conv >= mxb::CONV_W4_F16) d->kb_per_group = p.gsize == 128 ? 2 : d->kblocks;  // fp16 slabs hold 64 k
@@ -316,13 +317,13 @@ int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* 
       return fail(rc, "problem %d: %s", i, m.c_str());
     }
   }
-  std::vector<int32_t> tprefix(static_cast<size_t>(P) + 1, 0);
-  int tc_problems = 0, stream_classes = 0;
-  const int rows_per_task = mxb::w4a16_stream_rows_per_task();
+  int tc_problems = 0, stream_classes = 0, stream_units = 0;
+  const int rows_per_group = mxb::w4a16_stream_rows_per_group();
   for (int i = 0; i < P; ++i) {
     const bool st_path = host[i].path != 0;
     if (st_path && host[i].K > stream_classes) stream_classes = host[i].K;  // largest K routed to the streaming kernel
-    tprefix[i + 1] = tprefix[i] + (st_path ? (host[i].N + rows_per_task - 1) / rows_per_task : 0);
+    // grid estimate only: the kernel builds the exact unit prefix from the device-resident row counts
+    if (st_path) stream_units += (host[i].N + rows_per_group - 1) / rows_per_group * (problems[i].m_range ? 1 : (problems[i].M + 15) / 16);
     if (!st_path && host[i].n_tiles > 0 && !(problems[i].M == 0 && !problems[i].m_range)) ++tc_problems;
   }
   Plan* slot = nullptr;
@@ -337,16 +338,12 @@ int get_plan(mxb_context* c, const MxbProblem* problems, int P, int32_t* const* 
   }
   if (slot->cap < size_t(P)) {
     if (slot->dev) cudaFree(slot->dev);
-    if (slot->task_prefix) cudaFree(slot->task_prefix);
     slot->dev = nullptr;
-    slot->task_prefix = nullptr;
     slot->cap = 0;
     CU_OK(cudaMalloc(reinterpret_cast<void**>(&slot->dev), sizeof(mxb::DevProblem) * size_t(P)));
-    CU_OK(cudaMalloc(reinterpret_cast<void**>(&slot->task_prefix), sizeof(int32_t) * (size_t(P) + 1)));
     slot->cap = size_t(P);
   }
-  CU_OK(cudaMemcpyAsync(slot->task_prefix, tprefix.data(), sizeof(int32_t) * (size_t(P) + 1), cudaMemcpyHostToDevice, st));
-  slot->stream_tasks = tprefix[P];
+  slot->stream_tasks = stream_units;
   slot->tc_problems = tc_problems;
   slot->stream_classes = stream_classes;
   slot->paired = paired;
@@ -386,7 +383,7 @@ int group_gemm_impl(mxb_context* c, const MxbProblem* problems, int P, int32_t* 
     }
     CU_OK(cudaEventRecord(c->ev_join, tc_st));
   }
-  if (pl->stream_tasks > 0) mxb::w4a16_stream_launch(pl->dev, P, pl->task_prefix, pl->stream_tasks, pl->stream_classes, st);
+  if (pl->stream_tasks > 0) mxb::w4a16_stream_launch(pl->dev, P, pl->stream_tasks, pl->stream_classes, c->sm_count, st);
   if (both) CU_OK(cudaStreamWaitEvent(st, c->ev_join, 0));
   if (pl->tc_problems > 0 && !both) {
     for (int off = 0; off < P; off += mxb::GG_MAXP) {
@@ -460,7 +457,6 @@ int mxb_destroy(mxb_handle_t c) {
   cudaDeviceSynchronize();
   for (auto& pl : c->plans) {
     if (pl.dev) cudaFree(pl.dev);
-    if (pl.task_prefix) cudaFree(pl.task_prefix);
   }
   for (auto& t : c->tables)
     if (t.dev) cudaFree(t.dev);
@@ -778,7 +774,7 @@ extern "C" int mxb_select_tiles(mxb_handle_t c, const MxbProblem* problems, int 
     int rc = classify(p, &k);
     if (rc) return rc;
     MxbTileChoice t;
-    const bool stream = p.a_bits == 16 && p.w_bits == 4 && p.M <= 16 && p.K % 128 == 0 && p.N % 16 == 0 &&
+    const bool stream = p.a_bits == 16 && p.w_bits == 4 && p.M <= 64 && p.K % 128 == 0 && p.N % 16 == 0 &&
                         p.K <= mxb::w4a16_stream_max_k() && p.tile_n == 0;
     const bool pair = gemm_path != 1 && pair_eligible(p);
     const double w_bytes = double(p.N) * p.K * p.w_bits / 8.0;

@@ -70,8 +70,8 @@ constexpr int GG_SMEM_BYTES = 1024 /*align slack*/ + GG_STAGES * GG_STAGE_BYTES 
                               (3 * GG_MAXP + 4) * 4;
 
 void gg_launch(const DevProblem* probs, int P, int grid, cudaStream_t stream);
-void w4a16_stream_launch(const DevProblem* probs, int P, const int32_t* task_prefix_dev, int total_tasks, int max_k, cudaStream_t st);
-int w4a16_stream_rows_per_task();
+void w4a16_stream_launch(const DevProblem* probs, int P, int est_units, int max_k, int sm_count, cudaStream_t st);
+int w4a16_stream_rows_per_group();
 int w4a16_stream_max_k();
 int gg_configure();  // cudaFuncSetAttribute(max dynamic smem); returns cudaError_t as int
 

@@ -7,12 +7,18 @@
 // unpack per weight tile.
 //
 // B200 design:
-//   * a CTA (12 warps, one per SM) takes 384 weight rows of ONE problem; the problem's <= 16 activation rows are
-//     staged once in shared memory;
+//   * PERSISTENT: one CTA per SM (16 warps) owns a CONTIGUOUS run of the launch's (expert, 16-token pass, 16-row
+//     slab) work items, cut at slab granularity in a cost space (K-stages per slab) every CTA derives from the
+//     device-resident row counts, so a CTA mostly stays inside one expert: its <= 16 activation rows are staged in
+//     shared memory once per (expert, pass) with cp.async, and the weight pipeline never drains between slabs, passes
+//     or experts;
 //   * every warp streams 16-row slabs of the packed weights through its OWN ring of shared-memory stages filled by
 //     TMA (one 16-row x 128-byte box per stage, 128-byte swizzle, mbarrier transaction counts): no register
-//     staging, no cross-warp synchronisation, up to 16 KB in flight per warp.  (A first version used one 256-byte
-//     cp.async.bulk per row: the per-copy cost of the TMA unit capped it at ~1.2 TB/s.)
+//     staging, no cross-warp synchronisation.  Lane 0 of the warp is its producer and runs `stages` boxes ahead of
+//     the warp, across slab / pass / expert boundaries, from a small list of (expert, row-group range) entries the
+//     CTA builds in shared memory.  (A first version used one 256-byte cp.async.bulk per row: the per-copy cost of
+//     the TMA unit capped it at ~1.2 TB/s; the second one launched one CTA per 384 rows and paid the token fill, the
+//     problem search and the pipeline fill 4.7 times per SM.)
 //   * the WEIGHTS are the m16 operand of mma.sync.m16n8k16 and the tokens the n8 operand, so one MMA consumes
 //     8 weights per lane and the token fragment is ONE 16-byte shared load per 32-bit weight word;
 //   * dequantisation is the reference's arithmetic (0x6400 magic, q - bias exactly, w = hfma(q, scale, zp): one fp16
@@ -38,25 +44,41 @@ __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1
       : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
-constexpr int WS_WARPS = 12;
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+constexpr int WS_WARPS = 16;
 constexpr int WS_SLAB = 16;                       // weight rows per slab (the m16 of the MMA)
-constexpr int WS_SLABS_PER_CTA = 24;              // 384 weight rows per CTA task (two slabs per warp)
 constexpr int WS_STAGE_K = 256;                   // k per stage: 128 bytes of every row = one 2 KB TMA box (16 rows)
 constexpr int WS_ROW_PITCH = 128;                 // TMA SWIZZLE_128B: 16-byte chunk c of row r sits at chunk c ^ (r & 7)
 constexpr int WS_STAGE_BYTES = WS_SLAB * WS_ROW_PITCH;
 constexpr int WS_MAX_STAGES = 8;
+constexpr int WS_MAX_P = 1024;                   // problems per launch (the unit prefix lives in shared memory)
+constexpr int WS_MAX_ENT = 64;                    // (expert, group range) entries per list build
+
+// one entry of the CTA's work list: slabs [sb, se) of problem p for the 16-token pass starting at row m0; warp w takes
+// the slabs sb + ((w - woff) mod WS_WARPS) + j * WS_WARPS (woff continues the round-robin across entries)
+struct __align__(16) WsEntry {
+  int p, m0, M, row0;
+  int sb, se, woff, nst;
+};
 
 // one 32-bit word (8 unsigned 4-bit codes, nibble order k = 0,2,4,6,1,3,5,7) -> 4 half2 = k (0,1) (2,3) (4,5) (6,7)
 //   lo_bias = 1024 + bias, hi_bias = 64 + bias (bias 7 for symmetric codes, 0 for asymmetric)
-__device__ __forceinline__ void dequant_word(uint32_t w, __half2 lo_bias, __half2 hi_bias, __half2 sc, __half2 zp, uint32_t (&o)[4]) {
+//   magic = 0x64006400 arrives as a kernel argument: as a literal next to the literal mask, (w & mask) | magic costs two
+//   LOP3 (one immediate per instruction); from a register it is one
+__device__ __forceinline__ void dequant_word(uint32_t w, uint32_t magic, __half2 lo_bias, __half2 nhi_bias, __half2 sc, __half2 zp,
+                                             uint32_t (&o)[4]) {
   const __half2 sixteenth = __float2half2_rn(0.0625f);
   const uint32_t w8 = w >> 8;
-  uint32_t t0 = (w & 0x000F000Fu) | 0x64006400u, t1 = (w & 0x00F000F0u) | 0x64006400u;
-  uint32_t t2 = (w8 & 0x000F000Fu) | 0x64006400u, t3 = (w8 & 0x00F000F0u) | 0x64006400u;
+  uint32_t t0 = (w & 0x000F000Fu) | magic, t1 = (w & 0x00F000F0u) | magic;
+  uint32_t t2 = (w8 & 0x000F000Fu) | magic, t3 = (w8 & 0x00F000F0u) | magic;
   __half2 q0 = __hsub2(*reinterpret_cast<__half2*>(&t0), lo_bias);
-  __half2 q1 = __hfma2(*reinterpret_cast<__half2*>(&t1), sixteenth, __hneg2(hi_bias));
+  __half2 q1 = __hfma2(*reinterpret_cast<__half2*>(&t1), sixteenth, nhi_bias);
   __half2 q2 = __hsub2(*reinterpret_cast<__half2*>(&t2), lo_bias);
-  __half2 q3 = __hfma2(*reinterpret_cast<__half2*>(&t3), sixteenth, __hneg2(hi_bias));
+  __half2 q3 = __hfma2(*reinterpret_cast<__half2*>(&t3), sixteenth, nhi_bias);
   q0 = __hfma2(q0, sc, zp);
   q1 = __hfma2(q1, sc, zp);
   q2 = __hfma2(q2, sc, zp);
@@ -67,211 +89,405 @@ __device__ __forceinline__ void dequant_word(uint32_t w, __half2 lo_bias, __half
   o[3] = *reinterpret_cast<uint32_t*>(&q3);
 }
 
-}  // namespace
+// cost weights of a problem's passes: every pass but the last holds 16 tokens (weight 4), the last one 4 or 3
+__device__ __forceinline__ int ws_cost(int np, int M) { return np > 0 ? 4 * (np - 1) + (M - 16 * (np - 1) > 8 ? 4 : 3) : 0; }
+// first item (pass-major, slab-minor) that starts at or after cost offset c inside a problem
+__device__ __forceinline__ int ws_item_of(int c, int M, int nslab, int nst) {
+  const int np = (M + 15) >> 4;
+  const int full = 4 * (np - 1) * nslab * nst;  // cost of the 16-token passes before the last one
+  if (c <= full) return (c + 4 * nst - 1) / (4 * nst);
+  const int wl = (M - 16 * (np - 1) > 8 ? 4 : 3) * nst;
+  return (np - 1) * nslab + (c - full + wl - 1) / wl;
+}
+__device__ __forceinline__ int ws_first_slab(const WsEntry& e, int warp) { return e.sb + ((warp - e.woff) & (WS_WARPS - 1)); }
 
-namespace {
+// Producer cursor of one warp (only lane 0 uses it): the next stage to request.
+struct WsProd {
+  int i, slab, ks;
+  bool live;
+};
 
-// Problems are routed here by DevProblem::path == 1 (few rows per expert).  16 activation rows are resident at a time
-// (more rows re-stream the weights, which then come from L2).
-__global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const DevProblem* __restrict__ probs, int P,
-                                                                     const int32_t* __restrict__ task_prefix /*[P+1] CTA tasks*/,
-                                                                     int stages_in) {
-  extern __shared__ __align__(1024) uint8_t ws_smem_raw[];
-  uint8_t* ws_smem = ws_smem_raw + ((1024u - (smem_u32(ws_smem_raw) & 1023u)) & 1023u);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  const int stages = stages_in;
-  const int task = blockIdx.x;
-  int p = 0;
-  while (task >= task_prefix[p + 1]) ++p;
-  const DevProblem& d = probs[p];
-  if (d.path != 1) return;
-  int M = d.M, row0 = 0;
-  if (d.m_range != nullptr) {
-    row0 = d.m_range[0];
-    M = d.m_range[1] - row0;
+// first entry at or after c.i this warp has a slab in
+__device__ __forceinline__ void ws_prod_seek(WsProd& c, const WsEntry* ent, int n_ent, int warp) {
+  for (; c.i < n_ent; ++c.i) {
+    const WsEntry e = ent[c.i];
+    const int first = ws_first_slab(e, warp);
+    if (first < e.se) {
+      c.slab = first;
+      c.ks = 0;
+      c.live = true;
+      return;
+    }
   }
-  if (M <= 0) return;
-  const int N = d.N, K = d.K;
-  const int64_t lda = d.lda, ldc = d.ldc;
-  const __half* A = static_cast<const __half*>(d.A_ptr) + static_cast<int64_t>(row0) * lda;
-  const __half* sb = d.scale_b;
-  const bool sym = d.sym != 0;
-  const int gsz = d.gsize > 0 ? d.gsize : K;  // 128 or per-channel
-  const __half2 lo_bias = __float2half2_rn(sym ? 1031.f : 1024.f), hi_bias = __float2half2_rn(sym ? 71.f : 64.f);
-  __half* C = d.C + static_cast<int64_t>(row0) * ldc;
+  c.live = false;
+}
+__device__ __forceinline__ void ws_prod_advance(WsProd& c, const WsEntry* ent, int n_ent, int warp) {
+  const WsEntry e = ent[c.i];
+  if (++c.ks < e.nst) return;
+  c.ks = 0;
+  c.slab += WS_WARPS;
+  if (c.slab < e.se) return;
+  ++c.i;
+  ws_prod_seek(c, ent, n_ent, warp);
+}
 
-  const int pitchT = K * 2 + 64;                                 // token row pitch: consecutive rows 4 bank groups apart
-  uint8_t* tok = ws_smem;
-  const int tokb = (16 * pitchT + 1023) & ~1023;                 // the ring is 1024-byte aligned (swizzle atom)
-  uint8_t* ring = ws_smem + tokb + warp * stages * WS_STAGE_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(ws_smem + tokb + WS_WARPS * stages * WS_STAGE_BYTES) + warp * WS_MAX_STAGES;
-  if (lane < stages) mbar_init(&full[lane], 1);
-  fence_mbar_init();
-  __syncwarp();
+struct WsProblem {  // per-entry constants of the consumer
+  const __half* A;
+  __half* C;
+  const __half* sb;
+  int64_t lda, ldc;
+  int N, K, gsz;
+  bool sym;
+};
 
-  // this warp's slabs: slab0 + warp, + WS_WARPS, ... inside the CTA's slab window
-  const int slab0 = (task - task_prefix[p]) * WS_SLABS_PER_CTA;
-  const int slab_end = min(slab0 + WS_SLABS_PER_CTA, N / WS_SLAB);
-  const int nst = (K + WS_STAGE_K - 1) / WS_STAGE_K;               // stages per slab
-  const int my_slabs = slab0 + warp < slab_end ? (slab_end - slab0 - warp + WS_WARPS - 1) / WS_WARPS : 0;
-  const int total = my_slabs * nst;
-  uint32_t used = 0;             // stage uses so far (ring position and mbarrier parity)
+// One entry (16-token pass of one expert) for one warp: its slabs of [sb, se), K in 256-wide stages.
+template <bool TWO>
+__device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& e, int mp, const uint8_t* tok, int pitchT,
+                                            const uint8_t* ring, uint64_t* full, int stages, uint32_t& cslot, uint32_t& cphase, WsProd& prod,
+                                            uint32_t& pslot, const DevProblem* probs, const WsEntry* ent, int n_ent, int warp, int lane,
+                                            uint32_t magic) {
+  const int g = lane >> 2, t = lane & 3;
+  const int N = pb.N, K = pb.K;
+  const __half2 lo_bias = __float2half2_rn(pb.sym ? 1031.f : 1024.f), nhi_bias = __float2half2_rn(pb.sym ? -71.f : -64.f);
+  // loop-invariant lane offsets: weight chunks 2t, 2t+1 of rows g (and g+8: +1024) under the TMA 128-byte swizzle; token
+  // units c = 0..7 of the lane's 128-byte k-block under the fill's unit swizzle (u ^ ((u >> 3) & 3), and (u >> 3) & 3 == t
+  // for the unit block of lane t)
+  const int wo0 = g * WS_ROW_PITCH + (((2 * t) ^ g) << 4), wo1 = g * WS_ROW_PITCH + (((2 * t + 1) ^ g) << 4);
+  int x[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) x[c] = g * pitchT + ((c ^ t) << 4);
+  const int pitch8 = 8 * pitchT;
 
-  auto issue = [&](int i) {      // stage i of this pass: one TMA box of 16 rows x 128 B (bytes past K/2 are zero-filled)
-    if (lane != 0) return;
-    const int sl = i / nst, ks = i - sl * nst;
-    const int n = (slab0 + warp + sl * WS_WARPS) * WS_SLAB;
-    const int slot = (used + i) % stages;  // `used` is the value at the start of the pass
-    {
-      mbar_expect_tx(&full[slot], WS_STAGE_BYTES);
-      tma_load_2d(ring + slot * WS_STAGE_BYTES, &d.tmB, &full[slot], ks * (WS_STAGE_K / 2), n);
+  float acc0[4][4], acc1[TWO ? 4 : 1][4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      acc0[c][q] = 0.f;
+      if (TWO) acc1[TWO ? c : 0][q] = 0.f;
+    }
+  // scales of the next stage are fetched while the current one is multiplied; lane t needs the group of k = k0 + 64 t.
+  // The raw (scale, zero) words are kept as loaded and unpacked at the top of the NEXT stage.
+  uint32_t nraw0 = 0u, nraw1 = 0u;  // asym (scale | zero << 16), sym (scale)
+  auto load_scales = [&](int slab, int ks) {
+    nraw0 = nraw1 = 0u;  // lanes past K multiply by zero
+    const int kl = ks * WS_STAGE_K + t * 64;
+    if (kl >= K) return;
+    const int64_t gi = static_cast<int64_t>(pb.gsz == K ? 0 : kl >> 7) * N + slab * WS_SLAB + g;
+    if (pb.sym) {
+      nraw0 = __half_as_ushort(__ldg(pb.sb + gi));
+      nraw1 = __half_as_ushort(__ldg(pb.sb + gi + 8));
+    } else {
+      nraw0 = __ldg(reinterpret_cast<const uint32_t*>(pb.sb) + gi);
+      nraw1 = __ldg(reinterpret_cast<const uint32_t*>(pb.sb) + gi + 8);
     }
   };
-
-  for (int m0 = 0; m0 < M; m0 += 16) {  // normally one pass
-    const int mp = min(16, M - m0);
-    const bool two = mp > 8;
-    __syncthreads();  // previous pass done with the token rows
-    const int fill_rows = two ? 16 : 8;  // rows mp..fill_rows-1 are zero; rows 8..15 are never read when mp <= 8
-    for (int i = threadIdx.x; i < fill_rows * (K >> 3); i += WS_WARPS * 32) {
-      const int r = i / (K >> 3), c = i - r * (K >> 3);
-      uint4 v = make_uint4(0, 0, 0, 0);
-      if (r < mp) v = *reinterpret_cast<const uint4*>(A + static_cast<int64_t>(m0 + r) * lda + c * 8);
-      *reinterpret_cast<uint4*>(tok + r * pitchT + ((c ^ ((c >> 3) & 3)) << 4)) = v;  // unit swizzle: lanes t = 0..3 read distinct bank groups
-    }
-    const uint32_t used0 = used;
-    for (int i = 0; i < min(stages, total); ++i) issue(i);
-    __syncthreads();  // token rows visible to every warp
-
-    // four independent accumulator chains per token tile: 16 dependent MMAs per stage on one accumulator exposed the
-    // mma.sync latency (ncu: "wait" stalls), the chains are summed when the slab is written
-    float acc0[4][4], acc1[4][4];
-#pragma unroll
-    for (int c = 0; c < 4; ++c)
-#pragma unroll
-      for (int e = 0; e < 4; ++e) acc0[c][e] = acc1[c][e] = 0.f;
-    // scales of stage i are fetched while stage i-1 is multiplied (a global load on the critical path of every stage
-    // showed up as long-scoreboard stalls); lane t needs the group of k = k0 + 64 t
-    // The raw (scale, zero) words are kept as loaded and only unpacked at the top of the NEXT stage, so nothing
-    // waits on the global load inside the stage that issues it.
-    __half2 sc0, zp0, sc1, zp1;
-    uint32_t nraw0 = 0u, nraw1 = 0u;  // next stage: asym (scale | zero << 16), sym (scale)
-    auto load_scales = [&](int sl, int ks) {
-      nraw0 = nraw1 = 0u;  // lanes past K (and stages past the end) multiply by zero
-      const int kl = ks * WS_STAGE_K + t * 64;
-      if (sl >= my_slabs || kl >= K) return;
-      const int64_t gi = static_cast<int64_t>(gsz == K ? 0 : kl >> 7) * N + (slab0 + warp + sl * WS_WARPS) * WS_SLAB + g;
-      if (sym) {
-        nraw0 = __half_as_ushort(sb[gi]);
-        nraw1 = __half_as_ushort(sb[gi + 8]);
-      } else {
-        nraw0 = *reinterpret_cast<const uint32_t*>(sb + gi * 2);
-        nraw1 = *reinterpret_cast<const uint32_t*>(sb + (gi + 8) * 2);
-      }
-    };
-    load_scales(0, 0);
-    int sl = 0, ks = 0;  // slab of this warp and k-stage inside it (no divisions in the loop)
-    for (int i = 0; i < total; ++i) {
-      const int n0 = (slab0 + warp + sl * WS_WARPS) * WS_SLAB;
-      const int k0 = ks * WS_STAGE_K;
-      {
-        const __half2 r0 = *reinterpret_cast<const __half2*>(&nraw0), r1 = *reinterpret_cast<const __half2*>(&nraw1);
-        sc0 = __half2half2(__low2half(r0));
-        sc1 = __half2half2(__low2half(r1));
-        zp0 = __half2half2(__high2half(r0));  // zero for symmetric codes (upper half of the raw word is 0)
-        zp1 = __half2half2(__high2half(r1));
-      }
-      const int ks_n = ks + 1 == nst ? 0 : ks + 1, sl_n = ks + 1 == nst ? sl + 1 : sl;
-      load_scales(sl_n, ks_n);
-      const uint32_t u = used0 + i;
-      const int slot = u % stages;
-      mbar_wait(&full[slot], (u / stages) & 1);
-      const uint8_t* st = ring + slot * WS_STAGE_BYTES;
-      // lane t owns the 16-byte chunks 2t, 2t+1 of rows g and g+8 (k = k0 + 64 t .. + 64): under the XOR swizzle the
-      // eight lanes of a quarter-warp then hit eight distinct bank groups.  K % 128 == 0, so a lane's 64 k are all
-      // inside K or all in the zero-filled tail of the box; tail lanes run with zero scales on in-range token addresses.
-      const int kl = min(k0 + t * 64, K - 64);
-      const uint8_t* tk = tok + g * pitchT;
-      const int u0 = kl >> 3;  // first 16-byte token unit of this lane
+  const int slab0 = ws_first_slab(e, warp);
+  if (slab0 < e.se) load_scales(slab0, 0);
+  for (int slab = slab0; slab < e.se; slab += WS_WARPS) {
+    const int n0 = slab * WS_SLAB;
+    for (int ks = 0; ks < e.nst; ++ks) {
+      const __half2 r0 = *reinterpret_cast<const __half2*>(&nraw0), r1 = *reinterpret_cast<const __half2*>(&nraw1);
+      const __half2 sc0 = __half2half2(__low2half(r0)), sc1 = __half2half2(__low2half(r1));
+      const __half2 zp0 = __half2half2(__high2half(r0)), zp1 = __half2half2(__high2half(r1));  // zero for symmetric codes
+      if (ks + 1 < e.nst) load_scales(slab, ks + 1);
+      else if (slab + WS_WARPS < e.se) load_scales(slab + WS_WARPS, 0);
+      mbar_wait(&full[cslot], cphase);
+      const uint8_t* st = ring + cslot * WS_STAGE_BYTES;
+      // lane t owns the 16-byte chunks 2t, 2t+1 of rows g and g+8 (k = k0 + 64 t .. + 64).  K % 128 == 0, so a lane's
+      // 64 k are all inside K or all in the zero-filled tail of the box; tail lanes run with zero scales on in-range
+      // token addresses.
+      const int kl = min(ks * WS_STAGE_K + t * 64, K - 64);
+      const uint8_t* tkb = tok + (kl << 1);
 #pragma unroll
       for (int jj = 0; jj < 2; ++jj) {
-        const int pc = ((2 * t + jj) ^ g) << 4;  // physical chunk of logical chunk 2t+jj in rows g and g+8
-        const uint4 wl = *reinterpret_cast<const uint4*>(st + g * WS_ROW_PITCH + pc);
-        const uint4 wh = *reinterpret_cast<const uint4*>(st + (g + 8) * WS_ROW_PITCH + pc);
+        const uint4 wl = *reinterpret_cast<const uint4*>(st + (jj ? wo1 : wo0));
+        const uint4 wh = *reinterpret_cast<const uint4*>(st + (jj ? wo1 : wo0) + 8 * WS_ROW_PITCH);
         const uint32_t wlw[4] = {wl.x, wl.y, wl.z, wl.w}, whw[4] = {wh.x, wh.y, wh.z, wh.w};
 #pragma unroll
         for (int wd = 0; wd < 4; ++wd) {  // word wd: k = kl + jj*32 + wd*8 .. +8
           uint32_t lo[4], hi[4];
-          dequant_word(wlw[wd], lo_bias, hi_bias, sc0, zp0, lo);
-          dequant_word(whw[wd], lo_bias, hi_bias, sc1, zp1, hi);
-          const int un = u0 + jj * 4 + wd;
-          const int off = (un ^ ((un >> 3) & 3)) << 4;  // token rows are stored with the same unit swizzle (see the fill)
-          const uint4 b = *reinterpret_cast<const uint4*>(tk + off);
+          dequant_word(wlw[wd], magic, lo_bias, nhi_bias, sc0, zp0, lo);
+          dequant_word(whw[wd], magic, lo_bias, nhi_bias, sc1, zp1, hi);
+          const uint8_t* ta = tkb + x[wd] + jj * 64;
+          const uint4 b = *reinterpret_cast<const uint4*>(ta);
           mma16816(acc0[wd], lo[0], hi[0], lo[1], hi[1], b.x, b.y);
           mma16816(acc0[(wd + 2) & 3], lo[2], hi[2], lo[3], hi[3], b.z, b.w);
-          if (two) {
-            const uint4 b2 = *reinterpret_cast<const uint4*>(tk + 8 * pitchT + off);
-            mma16816(acc1[wd], lo[0], hi[0], lo[1], hi[1], b2.x, b2.y);
-            mma16816(acc1[(wd + 2) & 3], lo[2], hi[2], lo[3], hi[3], b2.z, b2.w);
+          if (TWO) {
+            const uint4 b2 = *reinterpret_cast<const uint4*>(ta + pitch8);
+            mma16816(acc1[TWO ? wd : 0], lo[0], hi[0], lo[1], hi[1], b2.x, b2.y);
+            mma16816(acc1[TWO ? (wd + 2) & 3 : 0], lo[2], hi[2], lo[3], hi[3], b2.z, b2.w);
           }
         }
       }
       __syncwarp();  // every lane is done reading the slot
-      if (i + stages < total) issue(i + stages);
-      if (ks == nst - 1) {
-        // ---- fp16 output of this slab: weight rows n0+g / n0+g+8, tokens 2t, 2t+1 (+8)
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          float a[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            a[e] = h ? (acc1[0][e] + acc1[1][e]) + (acc1[2][e] + acc1[3][e]) : (acc0[0][e] + acc0[1][e]) + (acc0[2][e] + acc0[3][e]);
-          const int tk0 = h * 8 + 2 * t;
-          if (tk0 < mp) {
-            C[static_cast<int64_t>(m0 + tk0) * ldc + n0 + g] = __float2half_rn(a[0]);
-            C[static_cast<int64_t>(m0 + tk0) * ldc + n0 + g + 8] = __float2half_rn(a[2]);
-          }
-          if (tk0 + 1 < mp) {
-            C[static_cast<int64_t>(m0 + tk0 + 1) * ldc + n0 + g] = __float2half_rn(a[1]);
-            C[static_cast<int64_t>(m0 + tk0 + 1) * ldc + n0 + g + 8] = __float2half_rn(a[3]);
-          }
-        }
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-#pragma unroll
-          for (int e = 0; e < 4; ++e) acc0[c][e] = acc1[c][e] = 0.f;
+      if (lane == 0 && prod.live) {  // refill the slot just freed (the producer's next slot IS this one: ring order)
+        const WsEntry pe = ent[prod.i];
+        mbar_expect_tx(&full[pslot], WS_STAGE_BYTES);
+        tma_load_2d(const_cast<uint8_t*>(ring) + pslot * WS_STAGE_BYTES, &probs[pe.p].tmB, &full[pslot], prod.ks * (WS_STAGE_K / 2),
+                    prod.slab * WS_SLAB);
+        if (++pslot == static_cast<uint32_t>(stages)) pslot = 0;
+        ws_prod_advance(prod, ent, n_ent, warp);
       }
-      ks = ks_n;
-      sl = sl_n;
+      if (++cslot == static_cast<uint32_t>(stages)) {
+        cslot = 0;
+        cphase ^= 1u;
+      }
     }
-    used = used0 + total;
+    // ---- fp16 output of this slab: weight rows n0+g / n0+g+8, tokens 2t, 2t+1 (+8)
+    __half* C = pb.C + static_cast<int64_t>(e.m0) * pb.ldc + n0 + g;
+#pragma unroll
+    for (int h = 0; h < (TWO ? 2 : 1); ++h) {
+      float a[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        a[q] = h ? (acc1[TWO ? 0 : 0][q] + acc1[TWO ? 1 : 0][q]) + (acc1[TWO ? 2 : 0][q] + acc1[TWO ? 3 : 0][q])
+                 : (acc0[0][q] + acc0[1][q]) + (acc0[2][q] + acc0[3][q]);
+      }
+      const int tk0 = h * 8 + 2 * t;
+      if (tk0 < mp) {
+        C[static_cast<int64_t>(tk0) * pb.ldc] = __float2half_rn(a[0]);
+        C[static_cast<int64_t>(tk0) * pb.ldc + 8] = __float2half_rn(a[2]);
+      }
+      if (tk0 + 1 < mp) {
+        C[static_cast<int64_t>(tk0 + 1) * pb.ldc] = __float2half_rn(a[1]);
+        C[static_cast<int64_t>(tk0 + 1) * pb.ldc + 8] = __float2half_rn(a[3]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        acc0[c][q] = 0.f;
+        if (TWO) acc1[TWO ? c : 0][q] = 0.f;
+      }
   }
 }
 
-int ws_smem_bytes(int K, int* stages_out) {
-  const int tokb = (16 * (K * 2 + 64) + 1023) & ~1023;
-  int stages = (227 * 1024 - 2048 - tokb - WS_WARPS * WS_MAX_STAGES * 8) / (WS_WARPS * WS_STAGE_BYTES);
+// Problems are routed here by DevProblem::path == 1 (few rows per expert).  16 activation rows are resident at a time
+// (more rows re-stream the CTA's slabs, which then come from L2).
+//
+// Work split: an item = (problem, 16-token pass, 16-row slab), items ordered problem-major, pass, slab; an item costs the
+// problem's K-stages x 3, or x 4 when the pass holds more than 8 tokens (two n8 MMA tiles per weight fragment: measured
+// 1.33x per stage).  Every CTA computes the same cost prefix over the problems from the DEVICE-resident row counts
+// (like the tcgen05 kernels build their tile prefix) and takes the items of an equal slice of the total cost, so empty
+// experts cost nothing, an expert with 40 rows weighs three passes, K = 2816 weighs twice K = 1408, and the static
+// contiguous split stays balanced to one slab whatever the routing was.
+__global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const DevProblem* __restrict__ probs, int P, int stages,
+                                                                     int tok_bytes, uint32_t magic) {
+  extern __shared__ __align__(1024) uint8_t ws_smem_raw[];
+  uint8_t* ws_smem = ws_smem_raw + ((1024u - (smem_u32(ws_smem_raw) & 1023u)) & 1023u);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* tok = ws_smem;
+  uint8_t* ring = ws_smem + tok_bytes + warp * stages * WS_STAGE_BYTES;
+  uint8_t* tail = ws_smem + tok_bytes + WS_WARPS * stages * WS_STAGE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(tail) + warp * WS_MAX_STAGES;
+  WsEntry* ent = reinterpret_cast<WsEntry*>(tail + WS_WARPS * WS_MAX_STAGES * 8);
+  int* ctl = reinterpret_cast<int*>(ent + WS_MAX_ENT);  // [0] entries in the list, [1] next problem, [2] list is the last one
+  int* cost_prefix = ctl + 4;                           // [P+1]
+  int* rows_of = cost_prefix + P + 1;                     // [P] rows of every problem (as read for the prefix)
+  if (lane < stages) mbar_init(&full[lane], 1);
+  fence_mbar_init();
+
+  for (int i = threadIdx.x; i < P; i += WS_WARPS * 32) {
+    const DevProblem& d = probs[i];
+    int M = d.M;
+    if (d.m_range != nullptr) M = d.m_range[1] - d.m_range[0];
+    const int np = (d.path == 1 && M > 0) ? (M + 15) >> 4 : 0;
+    rows_of[i] = np > 0 ? M : 0;
+    cost_prefix[i + 1] = ws_cost(np, M) * (d.N / WS_SLAB) * ((d.K + WS_STAGE_K - 1) / WS_STAGE_K);
+  }
+  __syncthreads();
+  if (warp == 0) {  // inclusive scan, 32 problems per step
+    int carry = 0;
+    for (int base = 0; base < P; base += 32) {
+      int v = base + lane < P ? cost_prefix[base + lane + 1] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += u;
+      }
+      if (base + lane < P) cost_prefix[base + lane + 1] = v + carry;
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+    if (lane == 0) cost_prefix[0] = 0;
+  }
+  __syncthreads();
+  // this CTA's contiguous share of the cost
+  const int U = cost_prefix[P];
+  const int u_lo = static_cast<int>(static_cast<int64_t>(blockIdx.x) * U / gridDim.x);
+  const int u_hi = static_cast<int>(static_cast<int64_t>(blockIdx.x + 1) * U / gridDim.x);
+  if (u_lo >= u_hi) return;
+
+  int p_next = 0;
+  {  // last problem whose cost range starts at or before u_lo
+    int lo = 0, hi = P;  // invariant: cost_prefix[lo] <= u_lo < cost_prefix[hi]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (cost_prefix[mid] <= u_lo) lo = mid;
+      else hi = mid;
+    }
+    p_next = lo;
+  }
+  uint32_t cslot = 0, cphase = 0, pslot = 0;
+
+  for (;;) {
+    __syncthreads();  // the previous list is fully consumed
+    if (warp == 0) {
+      // One lane per problem: the items [ia, ib) of the problem inside this CTA's cost slice (a boundary inside an item
+      // rounds up, identically in both neighbours), one entry per pass they touch.
+      int n = 0, base = p_next, nxt = -1, slabs_before = 0;
+      bool last = false;
+      while (n < WS_MAX_ENT && !last) {
+        const int p = base + lane;
+        const bool inr = p < P && cost_prefix[min(p, P)] < u_hi;
+        int ia = 0, ib = 0, nslab = 1, nst = 1, M = 0, row0 = 0;
+        if (inr) {
+          const int pre = cost_prefix[p], pre1 = cost_prefix[p + 1];
+          if (pre1 > pre) {
+            const DevProblem& d = probs[p];
+            nst = (d.K + WS_STAGE_K - 1) / WS_STAGE_K;
+            nslab = d.N / WS_SLAB;
+            M = rows_of[p];
+            if (d.m_range != nullptr) row0 = d.m_range[0];
+            ia = ws_item_of(max(u_lo, pre) - pre, M, nslab, nst);
+            ib = ws_item_of(min(u_hi, pre1) - pre, M, nslab, nst);
+          }
+        }
+        const bool has = ib > ia;
+        const int pa = ia / nslab, pb = has ? (ib - 1) / nslab : pa;
+        const int cnt = has ? pb - pa + 1 : 0;
+        int pos = cnt, sl = ib - ia;  // exclusive scans of the entry counts and the slab counts
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int u = __shfl_up_sync(0xffffffffu, pos, o), v = __shfl_up_sync(0xffffffffu, sl, o);
+          if (lane >= o) {
+            pos += u;
+            sl += v;
+          }
+        }
+        const int tot_cnt = __shfl_sync(0xffffffffu, pos, 31), tot_sl = __shfl_sync(0xffffffffu, sl, 31);
+        pos = n + pos - cnt;
+        sl = slabs_before + sl - (ib - ia);
+        const bool fits = pos + cnt <= WS_MAX_ENT;
+        if (has && fits) {
+          for (int ps = pa; ps <= pb; ++ps) {
+            WsEntry e;
+            e.p = p;
+            e.m0 = ps * 16;
+            e.M = M;
+            e.row0 = row0;
+            e.sb = ps == pa ? ia - pa * nslab : 0;
+            e.se = ps == pb ? ib - pb * nslab : nslab;
+            e.woff = sl & (WS_WARPS - 1);
+            e.nst = nst;
+            sl += e.se - e.sb;
+            ent[pos++] = e;
+          }
+        }
+        const unsigned over = __ballot_sync(0xffffffffu, has && !fits);
+        const unsigned im = __ballot_sync(0xffffffffu, inr);
+        if (over) {  // list full: resume at the first problem that did not fit (lanes after it did not write: pos is monotone)
+          const int first = __ffs(over) - 1;
+          nxt = base + first;
+          n = __shfl_sync(0xffffffffu, pos, first);
+          break;
+        }
+        n += tot_cnt;
+        slabs_before += tot_sl;
+        if (im != 0xffffffffu) last = true;
+        else base += 32;
+      }
+      if (lane == 0) {
+        ctl[0] = n;
+        ctl[1] = nxt >= 0 ? nxt : base;  // `base` has moved past every problem looked at unless `last`
+        ctl[2] = (last && nxt < 0) ? 1 : 0;
+      }
+    }
+    __syncthreads();
+    const int n_ent = ctl[0];
+    const bool last_list = ctl[2] != 0;
+    p_next = ctl[1];
+
+    // producer: request the first `stages` boxes of this list
+    WsProd prod = {0, 0, 0, false};
+    if (lane == 0) {
+      ws_prod_seek(prod, ent, n_ent, warp);
+      for (int s = 0; s < stages && prod.live; ++s) {
+        const WsEntry pe = ent[prod.i];
+        mbar_expect_tx(&full[pslot], WS_STAGE_BYTES);
+        tma_load_2d(ring + pslot * WS_STAGE_BYTES, &probs[pe.p].tmB, &full[pslot], prod.ks * (WS_STAGE_K / 2), prod.slab * WS_SLAB);
+        if (++pslot == static_cast<uint32_t>(stages)) pslot = 0;
+        ws_prod_advance(prod, ent, n_ent, warp);
+      }
+    }
+
+    for (int i = 0; i < n_ent; ++i) {
+      const WsEntry e = ent[i];
+      const DevProblem& d = probs[e.p];
+      WsProblem pb;
+      pb.N = d.N;
+      pb.K = d.K;
+      pb.lda = d.lda;
+      pb.ldc = d.ldc;
+      pb.A = static_cast<const __half*>(d.A_ptr) + static_cast<int64_t>(e.row0) * pb.lda;
+      pb.C = d.C + static_cast<int64_t>(e.row0) * pb.ldc;
+      pb.sb = d.scale_b;
+      pb.sym = d.sym != 0;
+      pb.gsz = d.gsize > 0 ? d.gsize : pb.K;
+      const int K = pb.K;
+      const int pitchT = K * 2 + 64;  // token row pitch: consecutive rows 4 bank groups apart
+      const int mp = min(16, e.M - e.m0);
+      const bool two = mp > 8;
+      __syncthreads();  // previous entry done with the token rows
+      const int fill_rows = two ? 16 : 8;  // rows mp..fill_rows-1 are zero; rows 8..15 are never read when mp <= 8
+      const int upr = K >> 3;              // 16-byte units per row
+      for (int idx = threadIdx.x; idx < fill_rows * upr; idx += WS_WARPS * 32) {
+        const int r = idx / upr, c = idx - r * upr;
+        uint8_t* dst = tok + r * pitchT + ((c ^ ((c >> 3) & 3)) << 4);  // unit swizzle: lanes t = 0..3 read distinct bank groups
+        if (r < mp) cp_async16(dst, pb.A + static_cast<int64_t>(e.m0 + r) * pb.lda + c * 8);
+        else *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+      }
+      cp_async_wait_all();
+      __syncthreads();  // token rows visible to every warp
+      if (two) ws_run_pass<true>(pb, e, mp, tok, pitchT, ring, full, stages, cslot, cphase, prod, pslot, probs, ent, n_ent, warp, lane, magic);
+      else ws_run_pass<false>(pb, e, mp, tok, pitchT, ring, full, stages, cslot, cphase, prod, pslot, probs, ent, n_ent, warp, lane, magic);
+    }
+    if (last_list) break;
+  }
+}
+
+int ws_smem_bytes(int K, int P, int* stages_out, int* tok_bytes_out) {
+  const int tokb = (16 * (K * 2 + 64) + 1023) & ~1023;  // the ring is 1024-byte aligned (swizzle atom)
+  const int fixed = WS_WARPS * WS_MAX_STAGES * 8 + WS_MAX_ENT * static_cast<int>(sizeof(WsEntry)) + 16 + (2 * P + 1) * 4 + 64;
+  int stages = (227 * 1024 - 1024 - tokb - fixed) / (WS_WARPS * WS_STAGE_BYTES);
   if (stages > WS_MAX_STAGES) stages = WS_MAX_STAGES;
   *stages_out = stages;
-  return tokb + WS_WARPS * stages * WS_STAGE_BYTES + WS_WARPS * WS_MAX_STAGES * 8 + 1024;
+  *tok_bytes_out = tokb;
+  return 1024 + tokb + WS_WARPS * stages * WS_STAGE_BYTES + fixed;
 }
 
 }  // namespace
 
+// est_units: host-side estimate of the work units (sizes the grid only; the kernel counts them from device-resident M)
 // max_k: largest K among the problems routed here (sizes the token staging and the ring depth)
-void w4a16_stream_launch(const DevProblem* probs, int P, const int32_t* task_prefix_dev, int total_tasks, int max_k, cudaStream_t st) {
-  if (total_tasks <= 0) return;
-  int stages = 0;
-  const int smem = ws_smem_bytes(max_k, &stages);
-  static int configured = 0;
-  if (configured < smem) {
+void w4a16_stream_launch(const DevProblem* probs, int P, int est_units, int max_k, int sm_count, cudaStream_t st) {
+  if (est_units <= 0) return;
+  static bool configured = false;
+  if (!configured) {
     cudaFuncSetAttribute(w4a16_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    configured = 227 * 1024;
+    configured = true;
   }
-  w4a16_stream_kernel<<<total_tasks, WS_WARPS * 32, smem, st>>>(probs, P, task_prefix_dev, stages);
+  const int grid = est_units < sm_count ? est_units : sm_count;
+  for (int off = 0; off < P; off += WS_MAX_P) {  // the prefix of one launch lives in shared memory
+    const int n = P - off < WS_MAX_P ? P - off : WS_MAX_P;
+    int stages = 0, tokb = 0;
+    const int smem = ws_smem_bytes(max_k, n, &stages, &tokb);
+    w4a16_stream_kernel<<<grid, WS_WARPS * 32, smem, st>>>(probs + off, n, stages, tokb, 0x64006400u);
+  }
 }
 
-int w4a16_stream_rows_per_task() { return WS_SLABS_PER_CTA * WS_SLAB; }
+int w4a16_stream_rows_per_group() { return WS_WARPS * WS_SLAB; }
 int w4a16_stream_max_k() { return 4096; }
 
 }  // namespace mxb
