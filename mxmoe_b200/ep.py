@@ -78,6 +78,28 @@ class EPMoELayer(MoELayer):
         self.counts_all = torch.zeros(self.W, E, dtype=torch.int32, device=d)
         self._last_seg = None
         self._build_segment_problems()
+        # MXB_EP_TIMING=1: CUDA events at the phase boundaries of forward(), read with timing_report()
+        import os
+        self._timing = os.environ.get("MXB_EP_TIMING", "0") == "1"
+        self._marks = []
+
+    def _mark(self, name: str):
+        if self._timing:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._marks.append((name, ev))
+
+    def timing_report(self):
+        """mean milliseconds per phase over the forwards recorded so far (synchronises)"""
+        torch.cuda.synchronize()
+        acc, cnt = {}, {}
+        for (n0, e0), (n1, e1) in zip(self._marks[:-1], self._marks[1:]):
+            if n1 == "start":
+                continue
+            acc[n1] = acc.get(n1, 0.0) + e0.elapsed_time(e1)
+            cnt[n1] = cnt.get(n1, 0) + 1
+        self._marks = []
+        return {k: acc[k] / cnt[k] for k in acc}
 
     # the parent's per-expert lists are replaced by per-(source, expert) segment lists
     def _build_problems(self):
@@ -103,10 +125,13 @@ class EPMoELayer(MoELayer):
     def forward(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: Optional[torch.Tensor] = None):
         h, T, k, E, W = self.h, x.shape[0], self.topk, self.E, self.W
         n_send = T * k
+        self._mark("start")
         offs, src, slot = h.permute(topk_ids, E)
         my_counts = (offs[1:] - offs[:-1]).contiguous()
         dist.all_gather_into_tensor(self.counts_all.view(-1), my_counts, group=self.group)
+        self._mark("permute+allgather")
         counts = self.counts_all.cpu().numpy()  # the one host sync of the step
+        self._mark("counts_to_host")
         send, recv, seg = ep_plan(counts, self.bounds, self.rank)
         n_recv = int(sum(recv))
         if n_recv > self.cap_rows:
@@ -122,11 +147,16 @@ class EPMoELayer(MoELayer):
             h.quant_act(x, src, n_send, None, [(16, -1)], False, None, self.send_f16, None)  # gather rows into sorted order
             self._a2a(self.recv_f16[:n_recv], self.send_f16[:n_send], recv, send)
             h.quant_act(self.recv_f16, None, n_recv, self.seg_offs, self._seg_actq_gu, False, self.x_q8, self.x_f16, self.x_sc)
+        self._mark("quant+dispatch_a2a")
         # ---- local experts on (source, expert) segments + the replicated shared expert on the local tokens
         self._run_segments(x, n_recv, T)
+        self._mark("experts")
         # ---- combine
         self._a2a(self.back[:n_send], self.dn_out[:n_recv], send, recv)
-        return h.combine(self.back, slot, topk_w, self.s_dn if self.ns else None, out)
+        self._mark("combine_a2a")
+        y = h.combine(self.back, slot, topk_w, self.s_dn if self.ns else None, out)
+        self._mark("combine")
+        return y
 
     def _run_segments(self, x: torch.Tensor, n_recv: int, T: int):
         h = self.h
