@@ -73,6 +73,9 @@ typedef struct MxbProblem {
   int32_t a_bits, w_bits, gsize, sym; /* gsize -1 = per-channel/per-token */
   int32_t tile_n;                     /* 0 = let the selector choose; else 64/128/256 */
   int32_t flags;                      /* MXB_EPI_* bits, 0 = plain GEMM */
+  const int32_t* c_row;               /* optional, with m_range: DEVICE int32 = first row of this problem in C when it is not
+                                         row_begin (C then is the base of a buffer laid out differently from A, e.g. the
+                                         result buffer of ANOTHER GPU mapped over NVLink: mxmoe_b200/ep.py); NULL = row_begin */
 } MxbProblem;
 
 /* Epilogue fusion of the step that follows the gate_up GEMM in the reference pipeline (silu_mul_then_quant,
@@ -111,6 +114,13 @@ const char* mxb_version(void);
  * corresponding choice at code-generation time from tile_config.json (mxmoe/kernels/tile_config.py:330-610).
  * The environment variable MXB_GEMM_PATH sets the initial value. */
 int mxb_set_gemm_path(mxb_handle_t h, int path);
+/* Number of SMs the handle's persistent kernels (GroupGEMM, streaming w4a16, Hadamard) occupy: `sms` CTAs instead of
+ * one per SM (rounded down to even; <= 0 or more than the device has restores the default).  A handle that runs
+ * next to NCCL kernels or to another handle's launches on a second stream leaves the remaining SMs to them — a
+ * persistent kernel that owns every SM would otherwise delay the collective until it exits (mxmoe_b200/ep.py runs
+ * the replicated shared expert this way under the dispatch/combine all-to-all).  The reference has one stream and
+ * no collectives (kernel_sketch.py:123). */
+int mxb_set_sm_limit(mxb_handle_t h, int sms);
 
 /* ---- piece (3)+(4): one launch over a mixed-precision problem list ---- */
 /* `problems` is a HOST array.  Plans (tile tables, tensor maps) are cached in the handle keyed by its content. */
@@ -148,6 +158,30 @@ int mxb_quant_act(mxb_handle_t h, const void* x, int H, const int32_t* src_row, 
 int mxb_silu_mul_quant(mxb_handle_t h, const void* gate_up, int I, int n_rows, const int32_t* expert_offsets,
                        const MxbActQ* actq, int E, int hadamard, void* out_q8, void* out_f16, void* scales,
                        int scale_cols, void* stream);
+
+/* ---- expert-parallel exchange over peer memory (no counterpart in the reference, which is single-GPU; BASELINE north_star:
+ * "sharding experts ... token dispatch and combine").  Rank r owns the experts [r*E/W, (r+1)*E/W).  Buffers reached through
+ * the peer_* tables are device allocations of the OTHER ranks mapped into this process (CUDA IPC / symmetric memory);
+ * entry [p] is rank p's buffer, entry [rank] the local one.  All three calls are stream-ordered and never synchronise. */
+typedef struct MxbRowDest { /* where the rows of one expert go: written on the device by mxb_ep_plan */
+  void* q8;      /* int8 containers [.., H] of the owning rank (or NULL) */
+  void* f16;     /* fp16 rows [.., H] of the owning rank (or NULL) */
+  void* scales;  /* fp16 [.., scale_cols] of the owning rank (or NULL) */
+  int64_t row0;  /* first row of this (source rank, expert) segment in those buffers */
+} MxbRowDest;
+/* counts of this rank (expert_offsets[e+1]-expert_offsets[e]) -> row `rank` of every rank's [W,E] int32 count matrix.
+ * peer_counts: HOST array of W device pointers. */
+int mxb_ep_push_counts(mxb_handle_t h, const int32_t* expert_offsets, int E, void* const* peer_counts, int W, int rank, void* stream);
+/* From the complete count matrix (after a cross-rank barrier): dest[E] = where each of my experts' rows go (segments on
+ * the owner are ordered source-rank-major, expert-minor); seg_offs[W*EL+1] = prefix of the segments I receive;
+ * back_row[W*EL] = first row of every received segment in its SOURCE rank's expert-sorted order (the c_row of its down
+ * GEMM).  peer_q8 / peer_f16 / peer_scales: HOST arrays of W device pointers, any may be NULL. */
+int mxb_ep_plan(mxb_handle_t h, const int32_t* counts_all, int W, int rank, int E, void* const* peer_q8, void* const* peer_f16,
+                void* const* peer_scales, int32_t* seg_offs, int32_t* back_row, MxbRowDest* dest, void* stream);
+/* mxb_quant_act whose output rows are scattered to their owners: row r of expert e -> dest[e] at row0 + (r - offsets[e]).
+ * max_ctas > 0 caps the grid (the kernel is NVLink-bound; leave SMs to whatever runs beside it). */
+int mxb_quant_act_push(mxb_handle_t h, const void* x, int H, const int32_t* src_row, int n_rows, const int32_t* expert_offsets,
+                       const MxbActQ* actq, int E, const MxbRowDest* dest, int scale_cols, int max_ctas, void* stream);
 
 /* ---- piece (5): gather + top-k weighted combine ---- */
 /* out[t] = fp16( sum_j topk_w[t,j] * down_out[slot_of[t,j]] (+ shared_out[t]) ), fp32 accumulation in j order. */

@@ -73,7 +73,8 @@ struct DevTable {  // small constant tables mirrored on the device, keyed by con
 
 struct mxb_context {
   int device = 0;
-  int sm_count = 0;
+  int sm_count = 0;  // CTAs the persistent kernels launch (mxb_set_sm_limit; default = every SM)
+  int sm_phys = 0;
   int gemm_path = 0;  // 0 = choose per problem list, 1 = single-CTA kernel, 2 = CTA-pair kernel (error if not eligible)
   EncodeTiledFn encode = nullptr;
   std::vector<Plan> plans;
@@ -192,6 +193,8 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   d->C = static_cast<__half*>(p.C);
   d->acc_out = acc_out;
   d->m_range = p.m_range;
+  d->c_row = p.c_row;
+  if (p.c_row && !p.m_range) return fail(MXB_EINVAL, "c_row needs m_range (device-resident rows)");
   if (p.flags & ~MXB_EPI_SILU_MUL) return fail(MXB_EINVAL, "unknown problem flags 0x%x", p.flags);
   if ((p.flags & MXB_EPI_SILU_MUL) && !paired)
     return fail(MXB_EINVAL, "MXB_EPI_SILU_MUL is served by the CTA-pair kernel only (list not eligible, or gemm path 1)");
@@ -222,7 +225,7 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   // Up to 64 rows (four 16-token passes over L2-resident slabs) the streaming kernel still beats a 128-row UMMA tile
   // fed by the converter warps, and a decode step's shared expert then rides in the same launch.
   const int m_cap = p.m_range ? (p.M <= 512 ? 16 : p.M) : p.M;
-  d->path = (!paired && k.conv == mxb::CONV_W4_F16 && m_cap <= 64 && p.K % 128 == 0 && p.N % 16 == 0 && p.K <= mxb::w4a16_stream_max_k() &&
+  d->path = (!paired && !p.c_row && k.conv == mxb::CONV_W4_F16 && m_cap <= 64 && p.K % 128 == 0 && p.N % 16 == 0 && p.K <= mxb::w4a16_stream_max_k() &&
              p.tile_n == 0) ? 1 : 0;
   if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k
   else if (k.conv >= mxb::CONV_W4_F16) d->kb_per_group = p.gsize == 128 ? 2 : d->kblocks;  // fp16 slabs hold 64 k
@@ -414,6 +417,7 @@ int mxb_create(int device, mxb_handle_t* out) {
   if (!c) return fail(MXB_ENOMEM, "out of host memory");
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
+  c->sm_phys = c->sm_count;
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult qres;
   cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
@@ -472,6 +476,15 @@ int mxb_destroy(mxb_handle_t c) {
 }
 
 int mxb_sm_count(mxb_handle_t c) { return c ? c->sm_count : 0; }
+
+int mxb_set_sm_limit(mxb_handle_t c, int sms) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (sms <= 0 || sms > c->sm_phys) sms = c->sm_phys;
+  sms &= ~1;  // the CTA-pair kernel launches clusters of two
+  if (sms < 2) sms = 2;
+  c->sm_count = sms;
+  return MXB_OK;
+}
 
 int mxb_set_gemm_path(mxb_handle_t c, int path) {
   if (!c) return fail(MXB_EINVAL, "null handle");
@@ -612,7 +625,8 @@ int quant_common(mxb_context* c, bool silu, const void* x, int H, const int32_t*
     return MXB_OK;
   }
   const int64_t pitch = silu ? 2 * int64_t(H) : int64_t(H);
-  CU_OK(mxb::quant_rows_launch(silu, x, H, pitch, src_row, n_rows, expert_offsets, tab, E, out_q8, out_f16, scales, scale_cols, st));
+  CU_OK(mxb::quant_rows_launch(silu, x, H, pitch, src_row, n_rows, expert_offsets, tab, E, out_q8, out_f16, scales, scale_cols, nullptr,
+                               c->sm_count * 32, st));
   return MXB_OK;
 }
 
@@ -658,6 +672,57 @@ int native_layout(int w_bits, int a_bits) {
 }  // namespace
 
 extern "C" {
+
+// ---- expert-parallel exchange over peer memory
+int mxb_ep_push_counts(mxb_handle_t c, const int32_t* expert_offsets, int E, void* const* peer_counts, int W, int rank, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (!expert_offsets || !peer_counts || E < 1 || W < 1 || rank < 0 || rank >= W) return fail(MXB_EINVAL, "bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU_OK(cudaSetDevice(c->device));
+  void* dev = nullptr;
+  int rc = device_table(c, peer_counts, sizeof(void*) * size_t(W), st, &dev);
+  if (rc) return rc;
+  CU_OK(mxb::ep_push_counts_launch(expert_offsets, E, static_cast<int32_t* const*>(dev), W, rank, st));
+  return MXB_OK;
+}
+
+int mxb_ep_plan(mxb_handle_t c, const int32_t* counts_all, int W, int rank, int E, void* const* peer_q8, void* const* peer_f16,
+                void* const* peer_scales, int32_t* seg_offs, int32_t* back_row, MxbRowDest* dest, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (!counts_all || !seg_offs || !back_row || !dest || E < 1 || W < 1 || rank < 0 || rank >= W) return fail(MXB_EINVAL, "bad argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU_OK(cudaSetDevice(c->device));
+  void* tabs[3] = {nullptr, nullptr, nullptr};
+  void* const* src[3] = {peer_q8, peer_f16, peer_scales};
+  for (int i = 0; i < 3; ++i)
+    if (src[i]) {
+      int rc = device_table(c, src[i], sizeof(void*) * size_t(W), st, &tabs[i]);
+      if (rc) return rc;
+    }
+  static_assert(sizeof(MxbRowDest) == sizeof(mxb::RowDest), "MxbRowDest layout");
+  CU_OK(mxb::ep_plan_launch(counts_all, W, rank, E, static_cast<void* const*>(tabs[0]), static_cast<void* const*>(tabs[1]),
+                            static_cast<void* const*>(tabs[2]), seg_offs, back_row, reinterpret_cast<mxb::RowDest*>(dest), st));
+  return MXB_OK;
+}
+
+int mxb_quant_act_push(mxb_handle_t c, const void* x, int H, const int32_t* src_row, int n_rows, const int32_t* expert_offsets,
+                       const MxbActQ* actq, int E, const MxbRowDest* dest, int scale_cols, int max_ctas, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (!x || !actq || !dest || !expert_offsets || E < 1 || n_rows < 0) return fail(MXB_EINVAL, "bad argument");
+  if (H % 8 != 0) return fail(MXB_EINVAL, "row length %d must be a multiple of 8", H);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CU_OK(cudaSetDevice(c->device));
+  const int32_t* tab = nullptr;
+  int g128, anyq, anyf;
+  int rc = actq_table(c, actq, E, st, &tab, &g128, &anyq, &anyf);
+  if (rc) return rc;
+  if (g128 && (H % 128 != 0 || scale_cols < H / 128)) return fail(MXB_EINVAL, "gsize 128 needs H %% 128 == 0 and scale_cols >= H/128");
+  if (scale_cols < 1) scale_cols = 1;
+  // E == 1 still goes through the destination table: the kernel treats dest != null like a routed list
+  CU_OK(mxb::quant_rows_launch(false, x, H, H, src_row, n_rows, expert_offsets, tab, E, nullptr, nullptr, nullptr, scale_cols,
+                               reinterpret_cast<const mxb::RowDest*>(dest), max_ctas, st));
+  return MXB_OK;
+}
 
 int mxb_permute(mxb_handle_t c, const int32_t* topk_ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
                 int32_t* slot_of, void* stream) {

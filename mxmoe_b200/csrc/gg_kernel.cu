@@ -258,6 +258,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
       const int M = S.m_arr[w.p], N = d.N, bn = d.bn;
       const int row_in_prob = m_blk * GG_BM + q * 32 + lane;
       const int grow = S.row0[w.p] + row_in_prob;           // global row of this lane
+      const int crow = (d.c_row != nullptr ? __ldg(d.c_row) : S.row0[w.p]) + row_in_prob;  // its row in C (DevProblem::c_row)
       const bool row_ok = row_in_prob < M;
       const int rows_valid = M - (m_blk * GG_BM + q * 32);  // rows of this warp inside the problem
       const int n0 = n_blk * bn;
@@ -305,7 +306,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
               }
             }
           }
-          stage_and_store(stg, h, lane, C, ldc, grow - lane, rows_valid, col0, N);
+          stage_and_store(stg, h, lane, C, ldc, crow - lane, rows_valid, col0, N);
         }
         tc_fence_before();
         __syncwarp();
@@ -367,7 +368,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
             uint32_t h[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) h[j] = pack_half2(run[c + 2 * j], run[c + 2 * j + 1]);
-            stage_and_store(stg, h, lane, C, ldc, grow - lane, rows_valid, n0 + c, N);
+            stage_and_store(stg, h, lane, C, ldc, crow - lane, rows_valid, n0 + c, N);
           }
         }
       }

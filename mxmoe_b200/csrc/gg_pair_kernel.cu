@@ -297,6 +297,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       const int64_t ldc = d.ldc;
       const bool silu = (d.epi_flags & 1) != 0;
       const int grow0 = S.row0[t.p] + t.t0;  // global row of the tile's first token
+      // C may start at another row than A (DevProblem::c_row): results written straight into a peer GPU's buffer
+      const int crow0 = (d.c_row != nullptr ? __ldg(d.c_row) : S.row0[t.p]) + t.t0;
       __half* sa_buf = S.sa_stage + acc * GP_BT;
       __half2 sb2 = __float2half2_rn(1.f);
       if (epi == EPI_INT_ROWCOL) {
@@ -308,7 +310,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       // every tile, also the unscaled ones: keeps the eight warps within one tile of each other, which is what makes
       // the two-deep sa_stage buffer safe
       named_bar_sync(2, 256);
-      __half* Cp = d.C + static_cast<int64_t>(grow0) * ldc + n;
+      __half* Cp = d.C + static_cast<int64_t>(crow0) * ldc + n;
       int32_t* ao = d.acc_out != nullptr ? d.acc_out + static_cast<int64_t>(t.t0) * N + n : nullptr;
       mbar_wait(&S.tmem_full[acc], acc_phase);
       tc_fence_after();
@@ -347,7 +349,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
           // The pair swaps one value per two tokens; the even lane finishes token c+2j, the odd lane token c+2j+1, each
           // from the fp16-rounded gate/up the unfused GEMM would have stored (silu_mul_h: quant_common.cuh).
           const int odd = lane & 1;
-          __half* hp = d.C + static_cast<int64_t>(grow0 + c + odd) * ldc + (n >> 1);
+          __half* hp = d.C + static_cast<int64_t>(crow0 + c + odd) * ldc + (n >> 1);
 #pragma unroll
           for (int j = 0; j < 16; j += 2) {
             const uint32_t send = odd ? ((h[j] & 0xFFFFu) | (h[j + 1] << 16)) : ((h[j] >> 16) | (h[j + 1] & 0xFFFF0000u));

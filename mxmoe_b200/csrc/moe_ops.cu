@@ -144,46 +144,127 @@ cudaError_t permute_launch(const int32_t* ids, int T, int k, int E, int32_t* exp
 
 // ============================================================================ per-token quantization
 namespace {
-// One warp per output row.  SILU=false: x row gathered through src_row; SILU=true: row = [gate | up].
+// One warp per output row (grid-stride).  SILU=false: x row gathered through src_row; SILU=true: row = [gate | up].
+// dest != nullptr (expert-parallel dispatch over peer memory): row r of expert e is written to
+// dest[e].{q8,f16,scales} at row dest[e].row0 + (r - expert_offsets[e]) — buffers of another GPU, reached over NVLink.
 template <bool SILU>
 __global__ void __launch_bounds__(256) quant_rows_kernel(const __half* __restrict__ x, int H, int64_t in_pitch,
                                                           const int32_t* __restrict__ src_row, int n_rows,
                                                           const int32_t* __restrict__ expert_offsets,
                                                           const int2* __restrict__ actq, int E, int8_t* __restrict__ out_q8,
                                                           __half* __restrict__ out_f16, __half* __restrict__ scales,
-                                                          int scale_cols) {
+                                                          int scale_cols, const RowDest* __restrict__ dest) {
   const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (row >= n_rows) return;
-  int a_bits = actq[0].x, gsize = actq[0].y;
-  if (E > 1) {
-    if (row >= expert_offsets[E]) return;  // rows past the last expert are not owned by anyone
-    const int e = find_expert(expert_offsets, E, row);
-    a_bits = actq[e].x;
-    gsize = actq[e].y;
+  if (E > 1 || dest != nullptr) n_rows = min(n_rows, expert_offsets[E]);  // rows past the last expert are not owned by anyone
+  for (int row = blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += gridDim.x * 8) {
+    int a_bits = actq[0].x, gsize = actq[0].y;
+    int64_t orow = row;
+    int8_t* q8 = out_q8;
+    __half* f16 = out_f16;
+    __half* sc = scales;
+    if (E > 1 || dest != nullptr) {
+      const int e = E > 1 ? find_expert(expert_offsets, E, row) : 0;
+      a_bits = actq[E > 1 ? e : 0].x;
+      gsize = actq[E > 1 ? e : 0].y;
+      if (dest != nullptr) {
+        const RowDest d = dest[e];
+        q8 = static_cast<int8_t*>(d.q8);
+        f16 = static_cast<__half*>(d.f16);
+        sc = static_cast<__half*>(d.scales);
+        orow = d.row0 + (row - expert_offsets[e]);
+      }
+    }
+    const int64_t srow = src_row ? src_row[row] : row;
+    const __half* in = x + srow * in_pitch;
+    auto ld = [&](int i, float (&v)[8]) { load8<SILU>(in, H, i, v); };
+    quantize_row(ld, H, lane, a_bits, gsize, q8 ? q8 + orow * H : nullptr, f16 ? f16 + orow * H : nullptr,
+                 sc ? sc + orow * scale_cols : nullptr);
   }
-  const int64_t srow = src_row ? src_row[row] : row;
-  const __half* in = x + srow * in_pitch;
-  auto ld = [&](int i, float (&v)[8]) { load8<SILU>(in, H, i, v); };
-  quantize_row(ld, H, lane, a_bits, gsize, out_q8 ? out_q8 + static_cast<int64_t>(row) * H : nullptr,
-               out_f16 ? out_f16 + static_cast<int64_t>(row) * H : nullptr,
-               scales ? scales + static_cast<int64_t>(row) * scale_cols : nullptr);
 }
 }  // namespace
 
 cudaError_t quant_rows_launch(bool silu, const void* x, int H, int64_t in_pitch, const int32_t* src_row, int n_rows,
                               const int32_t* expert_offsets, const int32_t* actq_dev, int E, void* out_q8, void* out_f16,
-                              void* scales, int scale_cols, cudaStream_t st) {
+                              void* scales, int scale_cols, const RowDest* dest, int max_ctas, cudaStream_t st) {
   if (n_rows == 0) return cudaSuccess;
-  const int grid = (n_rows + 7) / 8;
+  int grid = (n_rows + 7) / 8;
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
   if (silu)
     quant_rows_kernel<true><<<grid, 256, 0, st>>>(static_cast<const __half*>(x), H, in_pitch, src_row, n_rows, expert_offsets,
                                                   reinterpret_cast<const int2*>(actq_dev), E, static_cast<int8_t*>(out_q8),
-                                                  static_cast<__half*>(out_f16), static_cast<__half*>(scales), scale_cols);
+                                                  static_cast<__half*>(out_f16), static_cast<__half*>(scales), scale_cols, dest);
   else
     quant_rows_kernel<false><<<grid, 256, 0, st>>>(static_cast<const __half*>(x), H, in_pitch, src_row, n_rows, expert_offsets,
                                                    reinterpret_cast<const int2*>(actq_dev), E, static_cast<int8_t*>(out_q8),
-                                                   static_cast<__half*>(out_f16), static_cast<__half*>(scales), scale_cols);
+                                                   static_cast<__half*>(out_f16), static_cast<__half*>(scales), scale_cols, dest);
+  return cudaGetLastError();
+}
+
+// ============================================================================ expert-parallel exchange plan
+namespace {
+// counts of this rank -> row `rank` of every peer's [W, E] count matrix (peer memory)
+__global__ void ep_push_counts_kernel(const int32_t* __restrict__ expert_offsets, int E, int32_t* const* __restrict__ peer_counts, int W,
+                                      int rank) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < W * E; i += gridDim.x * blockDim.x) {
+    const int p = i / E, e = i - p * E;
+    peer_counts[p][rank * E + e] = expert_offsets[e + 1] - expert_offsets[e];
+  }
+}
+
+__device__ __forceinline__ int ep_bound(int r, int E, int W) { return static_cast<int>(static_cast<int64_t>(r) * E / W); }
+
+// From the all-ranks count matrix: where my rows go (dest), how what I receive is laid out (seg_offs: source-major,
+// local-expert-minor, mxmoe_b200/ep.py ep_plan) and where every received segment's results return to (back_row:
+// the segment's first row in the SOURCE rank's expert-sorted order).
+__global__ void ep_plan_kernel(const int32_t* __restrict__ counts, int W, int rank, int E, void* const* __restrict__ peer_q8,
+                               void* const* __restrict__ peer_f16, void* const* __restrict__ peer_scales, int32_t* __restrict__ seg_offs,
+                               int32_t* __restrict__ back_row, RowDest* __restrict__ dest) {
+  const int lo = ep_bound(rank, E, W), hi = ep_bound(rank + 1, E, W), EL = hi - lo;
+  const int tid = threadIdx.x;
+  // dispatch destinations: expert e lives on rank p; my rows follow those of the ranks before me, experts in order
+  for (int e = tid; e < E; e += blockDim.x) {
+    int p = 0;
+    while (ep_bound(p + 1, E, W) <= e) ++p;
+    const int plo = ep_bound(p, E, W), phi = ep_bound(p + 1, E, W);
+    int64_t r0 = 0;
+    for (int s = 0; s < rank; ++s)
+      for (int q = plo; q < phi; ++q) r0 += counts[s * E + q];
+    for (int q = plo; q < e; ++q) r0 += counts[rank * E + q];
+    RowDest d;
+    d.q8 = peer_q8 ? peer_q8[p] : nullptr;
+    d.f16 = peer_f16 ? peer_f16[p] : nullptr;
+    d.scales = peer_scales ? peer_scales[p] : nullptr;
+    d.row0 = r0;
+    dest[e] = d;
+  }
+  // return rows: segment (s, i) = rows of source s for my expert lo+i; in s's sorted order they start after all of s's
+  // rows for experts before lo+i
+  for (int j = tid; j < W * EL; j += blockDim.x) {
+    const int s = j / EL, i = j - s * EL;
+    int r0 = 0;
+    for (int q = 0; q < lo + i; ++q) r0 += counts[s * E + q];
+    back_row[j] = r0;
+  }
+  __syncthreads();
+  if (tid == 0) {  // receive layout (W*EL <= a few hundred)
+    int acc = 0;
+    seg_offs[0] = 0;
+    for (int j = 0; j < W * EL; ++j) {
+      const int s = j / EL, i = j - s * EL;
+      acc += counts[s * E + lo + i];
+      seg_offs[j + 1] = acc;
+    }
+  }
+}
+}  // namespace
+
+cudaError_t ep_push_counts_launch(const int32_t* expert_offsets, int E, int32_t* const* peer_counts_dev, int W, int rank, cudaStream_t st) {
+  ep_push_counts_kernel<<<1, 256, 0, st>>>(expert_offsets, E, peer_counts_dev, W, rank);
+  return cudaGetLastError();
+}
+cudaError_t ep_plan_launch(const int32_t* counts, int W, int rank, int E, void* const* peer_q8, void* const* peer_f16,
+                           void* const* peer_scales, int32_t* seg_offs, int32_t* back_row, RowDest* dest, cudaStream_t st) {
+  ep_plan_kernel<<<1, 256, 0, st>>>(counts, W, rank, E, peer_q8, peer_f16, peer_scales, seg_offs, back_row, dest);
   return cudaGetLastError();
 }
 

@@ -350,6 +350,7 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
             nslab = d.N / WS_SLAB;
             M = rows_of[p];
             if (d.m_range != nullptr) row0 = d.m_range[0];
+            // (DevProblem::c_row is not honoured here: api.cu keeps such problems off this path)
             ia = ws_item_of(max(u_lo, pre) - pre, M, nslab, nst);
             ib = ws_item_of(min(u_hi, pre1) - pre, M, nslab, nst);
           }

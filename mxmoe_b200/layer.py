@@ -123,10 +123,10 @@ class MoELayer:
             self.s_dn = torch.empty(T, H, dtype=f16, device=d)
         self.offs = torch.zeros(self.EL + 1, dtype=torch.int32, device=d)
 
-    def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range, flags=0):
+    def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range, flags=0, c_row=None):
         A = A_f16 if q.a_bits >= 16 else A_q8
         return ops.Problem(A, B, C, rows, N, K, q.w_bits, q.a_bits, q.w_gsize, q.w_sym if q.w_bits < 16 else True,
-                           scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range, flags=flags)
+                           scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range, flags=flags, c_row=c_row)
 
     def _build_problems(self):
         """Marshal the two problem lists once; M of every routed expert is read on the device from self.offs."""

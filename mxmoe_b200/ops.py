@@ -36,11 +36,16 @@ class MxbProblem(C.Structure):
         ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
         ("a_bits", C.c_int32), ("w_bits", C.c_int32), ("gsize", C.c_int32), ("sym", C.c_int32),
         ("tile_n", C.c_int32), ("flags", C.c_int32),
+        ("c_row", C.c_void_p),
     ]
 
 
 class MxbActQ(C.Structure):
     _fields_ = [("a_bits", C.c_int32), ("gsize", C.c_int32)]
+
+
+class MxbRowDest(C.Structure):
+    _fields_ = [("q8", C.c_void_p), ("f16", C.c_void_p), ("scales", C.c_void_p), ("row0", C.c_int64)]
 
 
 class MxbTileChoice(C.Structure):
@@ -57,12 +62,16 @@ EXPORTS = [
     ("mxb_sm_count", _I, [_P]),
     ("mxb_version", C.c_char_p, []),
     ("mxb_set_gemm_path", _I, [_P, _I]),
+    ("mxb_set_sm_limit", _I, [_P, _I]),
     ("mxb_group_gemm", _I, [_P, C.POINTER(MxbProblem), _I, _P]),
     ("mxb_group_gemm_debug_acc", _I, [_P, C.POINTER(MxbProblem), _I, C.POINTER(_P), _P]),
     ("mxb_group_gemm_reflayout", _I, [_P] + [_P] * 14 + [_I, _P]),
     ("mxb_permute", _I, [_P, _P, _I, _I, _I, _P, _P, _P, _P]),
     ("mxb_quant_act", _I, [_P, _P, _I, _P, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),
     ("mxb_silu_mul_quant", _I, [_P, _P, _I, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),
+    ("mxb_ep_push_counts", _I, [_P, _P, _I, C.POINTER(_P), _I, _I, _P]),
+    ("mxb_ep_plan", _I, [_P, _P, _I, _I, _I, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), _P, _P, _P, _P]),
+    ("mxb_quant_act_push", _I, [_P, _P, _I, _P, _I, _P, C.POINTER(MxbActQ), _I, _P, _I, _I, _P]),
     ("mxb_combine", _I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _P]),
     ("mxb_quant_pack_weight", _I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     ("mxb_repack_from_ref", _I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
@@ -120,11 +129,12 @@ class Problem:
     ldc: int = 0
     tile_n: int = 0
     flags: int = 0  # EPI_SILU_MUL: B rows interleaved (gate_i, up_i), C = silu(gate)*up [M, N/2]
+    c_row: Optional[torch.Tensor] = None  # device int32: first row of the problem in C when it is not m_range[0]
 
     def to_c(self) -> MxbProblem:
         return MxbProblem(_ptr(self.A), _ptr(self.B), _ptr(self.scale_a), _ptr(self.scale_b), _ptr(self.C),
                           _ptr(self.m_range), self.lda, self.ldc, self.M, self.N, self.K, self.a_bits, self.w_bits,
-                          self.gsize, 1 if self.sym else 0, self.tile_n, self.flags)
+                          self.gsize, 1 if self.sym else 0, self.tile_n, self.flags, _ptr(self.c_row))
 
 
 class Handle:
@@ -160,6 +170,36 @@ class Handle:
     @property
     def sm_count(self) -> int:
         return self.lib.mxb_sm_count(self.h)
+
+    # ---------------------------------------------------------------- expert-parallel exchange over peer memory
+    @staticmethod
+    def _ptr_table(tensors):
+        if tensors is None:
+            return None
+        return (C.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+    def ep_push_counts(self, expert_offsets: torch.Tensor, E: int, peer_counts, rank: int):
+        """my per-expert counts -> row `rank` of every rank's [W, E] count matrix (peer_counts: one tensor per rank)"""
+        tab = self._ptr_table(peer_counts)
+        self._check(self.lib.mxb_ep_push_counts(self.h, expert_offsets.data_ptr(), E, tab, len(peer_counts), rank, _stream()),
+                    "mxb_ep_push_counts")
+
+    def ep_plan(self, counts_all: torch.Tensor, W: int, rank: int, E: int, peer_q8, peer_f16, peer_scales, seg_offs: torch.Tensor,
+                back_row: torch.Tensor, dest: torch.Tensor):
+        """dest: uint8 device tensor of E * sizeof(MxbRowDest) bytes, filled on the device"""
+        self._check(self.lib.mxb_ep_plan(self.h, counts_all.data_ptr(), W, rank, E, self._ptr_table(peer_q8), self._ptr_table(peer_f16),
+                                         self._ptr_table(peer_scales), seg_offs.data_ptr(), back_row.data_ptr(), dest.data_ptr(),
+                                         _stream()), "mxb_ep_plan")
+
+    def quant_act_push(self, x: torch.Tensor, src_row: Optional[torch.Tensor], n_rows: int, expert_offsets: torch.Tensor, actq,
+                       dest: torch.Tensor, scale_cols: int, max_ctas: int = 0):
+        arr = (MxbActQ * len(actq))(*[MxbActQ(a, g) for a, g in actq])
+        self._check(self.lib.mxb_quant_act_push(self.h, x.data_ptr(), x.shape[1], _ptr(src_row), n_rows, expert_offsets.data_ptr(), arr,
+                                                len(actq), dest.data_ptr(), scale_cols, max_ctas, _stream()), "mxb_quant_act_push")
+
+    def set_sm_limit(self, sms: int):
+        """CTAs of the persistent kernels (default one per SM); <= 0 restores the default."""
+        self._check(self.lib.mxb_set_sm_limit(self.h, int(sms)), "mxb_set_sm_limit")
 
     def set_gemm_path(self, path: int):
         """0 = auto (CTA-pair kernel when the whole list is eligible), 1 = single-CTA kernel, 2 = CTA-pair kernel."""
