@@ -222,7 +222,14 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    step = lambda: layer.forward(x, ids, w, out)
+    # decode-sized steps are launch-bound: the step is captured once as a CUDA graph (MoELayer.capture) and replayed
+    use_graph = world == 1 and T <= 256
+    if use_graph:
+        graph = layer.capture(x, ids, w, out)
+        step = graph.replay
+        cfg["step"] = "CUDA graph replay of layer.forward (decode)"
+    else:
+        step = lambda: layer.forward(x, ids, w, out)
     for _ in range(warmup):
         step()
     if world > 1 and os.environ.get("MXB_EP_TIMING", "0") == "1":
@@ -246,7 +253,7 @@ def main():
     # e2e: pinned host buffers in, pinned host buffer out, every step, through the public host-batch API
     # (mxmoe_b200.layer.HostPipeline: upload / kernels / download on three streams, two device slots)
     from mxmoe_b200.layer import HostPipeline
-    pipe = HostPipeline(layer, T)
+    pipe = HostPipeline(layer, T, graph=use_graph)
     out_hosts = [out_host, torch.empty_like(out_host).pin_memory()]
     n_sub = [0]
     def step_e2e():

@@ -76,6 +76,9 @@ typedef struct MxbProblem {
   const int32_t* c_row;               /* optional, with m_range: DEVICE int32 = first row of this problem in C when it is not
                                          row_begin (C then is the base of a buffer laid out differently from A, e.g. the
                                          result buffer of ANOTHER GPU mapped over NVLink: mxmoe_b200/ep.py); NULL = row_begin */
+  const int32_t* a_rows;              /* optional: DEVICE int32 per row of the problem's row range = the row of A to read (the
+                                         token gather of gg_permute_inp, ref_bind.cu:47-64, folded into the operand load).  A is
+                                         then the un-permuted [T, K] buffer.  Streaming (decode) path only. */
 } MxbProblem;
 
 /* Epilogue fusion of the step that follows the gate_up GEMM in the reference pipeline (silu_mul_then_quant,
@@ -86,6 +89,11 @@ typedef struct MxbProblem {
  * with the arithmetic of mxb_silu_mul_quant, so the result is bit-identical to the two-step path.
  * Served by the CTA-pair kernel only: a list that is not eligible for it (see mxb_set_gemm_path) is MXB_EINVAL. */
 #define MXB_EPI_SILU_MUL 1
+/* Prologue fusion for the DOWN projection of a decode step: A holds the gate_up output [M, 2K] = [gate | up] (default
+ * lda = 2K) and the kernel multiplies by act_fn(gate) * up, computed while the rows are staged, with the arithmetic of
+ * mxb_silu_mul_quant in fp16 mode (bit-identical to running it first).  Served by the streaming weight-only kernel only
+ * (w4a16, at most 64 rows, or device-resident rows with capacity <= 512); any other problem is MXB_EINVAL. */
+#define MXB_PRO_SILU_MUL 2
 
 /* Per-expert activation quantization parameters for mxb_quant_act / mxb_silu_mul_quant
  * (the reference's qparams_per_exp tuples, ref_bind.cu:321,365). */

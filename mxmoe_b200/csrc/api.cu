@@ -187,15 +187,16 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   if (k.epi != mxb::EPI_F32 && (!p.scale_a || !p.scale_b)) return fail(MXB_EINVAL, "quantized problem without scales");
   if (k.conv >= mxb::CONV_W4_F16 && !p.scale_b) return fail(MXB_EINVAL, "weight-only problem without scale_b");
   const int bn = paired ? 256 : pick_tile_n(p, k);
-  const int64_t lda = p.lda > 0 ? p.lda : p.K;
+  const int64_t lda = p.lda > 0 ? p.lda : ((p.flags & MXB_PRO_SILU_MUL) ? 2 * int64_t(p.K) : p.K);
   d->scale_a = static_cast<const __half*>(p.scale_a);
   d->scale_b = static_cast<const __half*>(p.scale_b);
   d->C = static_cast<__half*>(p.C);
   d->acc_out = acc_out;
   d->m_range = p.m_range;
   d->c_row = p.c_row;
+  d->a_rows = p.a_rows;
   if (p.c_row && !p.m_range) return fail(MXB_EINVAL, "c_row needs m_range (device-resident rows)");
-  if (p.flags & ~MXB_EPI_SILU_MUL) return fail(MXB_EINVAL, "unknown problem flags 0x%x", p.flags);
+  if (p.flags & ~(MXB_EPI_SILU_MUL | MXB_PRO_SILU_MUL)) return fail(MXB_EINVAL, "unknown problem flags 0x%x", p.flags);
   if ((p.flags & MXB_EPI_SILU_MUL) && !paired)
     return fail(MXB_EINVAL, "MXB_EPI_SILU_MUL is served by the CTA-pair kernel only (list not eligible, or gemm path 1)");
   d->epi_flags = p.flags;
@@ -227,6 +228,8 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   const int m_cap = p.m_range ? (p.M <= 512 ? 16 : p.M) : p.M;
   d->path = (!paired && !p.c_row && k.conv == mxb::CONV_W4_F16 && m_cap <= 64 && p.K % 128 == 0 && p.N % 16 == 0 && p.K <= mxb::w4a16_stream_max_k() &&
              p.tile_n == 0) ? 1 : 0;
+  if ((p.a_rows || (p.flags & MXB_PRO_SILU_MUL)) && d->path != 1)
+    return fail(MXB_EINVAL, "a_rows / MXB_PRO_SILU_MUL are served by the streaming w4a16 kernel only (decode-sized weight-only problems)");
   if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k
   else if (k.conv >= mxb::CONV_W4_F16) d->kb_per_group = p.gsize == 128 ? 2 : d->kblocks;  // fp16 slabs hold 64 k
   else d->kb_per_group = d->kblocks;

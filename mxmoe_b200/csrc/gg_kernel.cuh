@@ -53,6 +53,7 @@ struct alignas(128) DevProblem {
   int64_t lda;          // elements per row of A
   int32_t epi_flags;    // MXB_EPI_* (pair kernel): 1 = silu(gate)*up over interleaved weight rows, C is [M, N/2]
   const int32_t* c_row; // device int32: first row of this problem in C when it differs from m_range[0] (else null)
+  const int32_t* a_rows; // streaming path: row of A behind every row of the problem's range (token gather), or null
   CUtensorMap tmA2;     // pair kernel only: tokens with a 128-row box (tmA has the 32-row box for ragged tiles)
 };
 static_assert(sizeof(DevProblem) == 640, "DevProblem layout");

@@ -32,6 +32,7 @@
 
 #include "gg_kernel.cuh"
 #include "ptx.cuh"
+#include "quant_common.cuh"
 
 namespace mxb {
 namespace {
@@ -431,7 +432,9 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
       pb.K = d.K;
       pb.lda = d.lda;
       pb.ldc = d.ldc;
-      pb.A = static_cast<const __half*>(d.A_ptr) + static_cast<int64_t>(e.row0) * pb.lda;
+      const int32_t* a_rows = d.a_rows;
+      const bool pro_silu = (d.epi_flags & 2) != 0;  // MXB_PRO_SILU_MUL: A = [gate | up], rows become silu(gate) * up
+      pb.A = static_cast<const __half*>(d.A_ptr) + (a_rows ? 0 : static_cast<int64_t>(e.row0) * pb.lda);
       pb.C = d.C + static_cast<int64_t>(e.row0) * pb.ldc;
       pb.sb = d.scale_b;
       pb.sym = d.sym != 0;
@@ -446,8 +449,25 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
       for (int idx = threadIdx.x; idx < fill_rows * upr; idx += WS_WARPS * 32) {
         const int r = idx / upr, c = idx - r * upr;
         uint8_t* dst = tok + r * pitchT + ((c ^ ((c >> 3) & 3)) << 4);  // unit swizzle: lanes t = 0..3 read distinct bank groups
-        if (r < mp) cp_async16(dst, pb.A + static_cast<int64_t>(e.m0 + r) * pb.lda + c * 8);
-        else *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+        if (r < mp) {
+          // the token gather (a_rows) and act_fn(gate) * up (MXB_PRO_SILU_MUL) happen here, while the rows are staged
+          const int64_t ar = a_rows ? a_rows[e.row0 + e.m0 + r] : e.m0 + r;
+          const __half* srcp = pb.A + ar * pb.lda + c * 8;
+          if (pro_silu) {
+            const uint4 gq = ld_global_nc_v4(srcp), uq = ld_global_nc_v4(srcp + K);
+            const __half* gh = reinterpret_cast<const __half*>(&gq);
+            const __half* uh = reinterpret_cast<const __half*>(&uq);
+            uint4 o;
+            __half* oh = reinterpret_cast<__half*>(&o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) oh[j] = __float2half_rn(silu_mul_h(gh[j], uh[j]));
+            *reinterpret_cast<uint4*>(dst) = o;
+          } else {
+            cp_async16(dst, srcp);
+          }
+        } else {
+          *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+        }
       }
       cp_async_wait_all();
       __syncthreads();  // token rows visible to every warp

@@ -55,6 +55,14 @@ class MoELayer:
         # Fuse act_fn(gate)*up into the gate_up GEMM epilogue (MXB_EPI_SILU_MUL) when every problem of the launch is
         # one the CTA-pair kernel covers; otherwise the two-step path (GroupGEMM -> mxb_silu_mul_quant) runs.
         self.fused_silu = fuse_silu and all(self._pair_ok(qlayer.experts[str(e)].gate) for e in ids_all)
+        # Decode steps of weight-only 4-bit layers: the streaming kernel gathers the token rows itself (MxbProblem.a_rows)
+        # and applies act_fn(gate) * up while staging the down projection's rows (MXB_PRO_SILU_MUL), so the step is
+        # permute -> GroupGEMM -> GroupGEMM -> combine.  Eligibility mirrors the kernel choice in api.cu (path 1).
+        def _wonly4(q):
+            return q.w_bits == 4 and q.a_bits >= 16
+        self.stream_fused = (expert_ids is None and max_tokens <= 64 and max_tokens * topk <= 512 and H % 128 == 0 and I % 128 == 0
+                             and not hadamard_down
+                             and all(_wonly4(qlayer.experts[str(e)].gate) and _wonly4(qlayer.experts[str(e)].down) for e in ids_all))
         gen = torch.Generator(device=self.dev).manual_seed(seed)
         ids = self.local_experts + ([E] if ns else [])
         for e in ids:
@@ -122,11 +130,14 @@ class MoELayer:
             self.sh_sc = torch.empty(T, Is // 128 if s.q_dn.a_gsize == 128 else 1, dtype=f16, device=d) if s.q_dn.a_bits < 16 else None
             self.s_dn = torch.empty(T, H, dtype=f16, device=d)
         self.offs = torch.zeros(self.EL + 1, dtype=torch.int32, device=d)
+        self.src = torch.zeros(R, dtype=torch.int32, device=d)      # permute outputs live in fixed buffers: problem lists
+        self.slot = torch.zeros(T, k, dtype=torch.int32, device=d)  # (a_rows) and CUDA graphs keep their addresses
 
-    def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range, flags=0, c_row=None):
+    def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range, flags=0, c_row=None, a_rows=None):
         A = A_f16 if q.a_bits >= 16 else A_q8
         return ops.Problem(A, B, C, rows, N, K, q.w_bits, q.a_bits, q.w_gsize, q.w_sym if q.w_bits < 16 else True,
-                           scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range, flags=flags, c_row=c_row)
+                           scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range, flags=flags, c_row=c_row,
+                           a_rows=a_rows)
 
     def _build_problems(self):
         """Marshal the two problem lists once; M of every routed expert is read on the device from self.offs."""
@@ -135,6 +146,10 @@ class MoELayer:
         gu, dn = [], []
         for i, ew in enumerate(self.experts[:self.EL]):
             mr = self.offs[i:i + 2]
+            if self.stream_fused:  # gate_up is built per input buffer (A = x itself, _finalize_problems); down reads [gate | up]
+                dn.append(self._problem(ew.q_dn, None, self.gu_out, None, ew.dn_packed, ew.dn_scale, self.dn_out, R, H, I, mr,
+                                        flags=ops.PRO_SILU_MUL))
+                continue
             gu.append(self._problem(ew.q_gu, self.x_q8, self.x_f16, self.x_sc, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * I, H, mr,
                                     flags=ops.EPI_SILU_MUL if self.fused_silu else 0))
             dn.append(self._problem(ew.q_dn, self.h_q8, self.h_f16, self.h_sc, ew.dn_packed, ew.dn_scale, self.dn_out, R, H, I, mr))
@@ -144,7 +159,7 @@ class MoELayer:
     def _finalize_problems(self, T: int, x: torch.Tensor):
         # x itself is an operand only when the shared expert takes fp16 activations; lists are kept per (T, x) so that
         # callers alternating between input buffers (HostPipeline) do not re-marshal every step
-        key = (T, x.data_ptr() if (self.ns and self.experts[-1].q_gu.a_bits >= 16) else 0)
+        key = (T, x.data_ptr() if (self.stream_fused or (self.ns and self.experts[-1].q_gu.a_bits >= 16)) else 0)
         if self._T_built == key:
             return
         if not hasattr(self, "_lists"):
@@ -154,7 +169,17 @@ class MoELayer:
             self._T_built = key
             return
         gu, dn = list(self._gu_routed), list(self._dn_routed)
-        if self.ns:
+        if self.stream_fused:
+            R = self.max_tokens * self.topk
+            gu = [self._problem(ew.q_gu, None, x, None, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * self.I, self.H,
+                                self.offs[i:i + 2], a_rows=self.src) for i, ew in enumerate(self.experts[:self.EL])]
+        if self.ns and self.stream_fused:
+            s = self.experts[-1]
+            Is = self.I * self.ns
+            gu.append(self._problem(s.q_gu, None, x, None, s.gu_packed, s.gu_scale, self.s_gu, T, 2 * Is, self.H, None))
+            dn.append(self._problem(s.q_dn, None, self.s_gu, None, s.dn_packed, s.dn_scale, self.s_dn, T, self.H, Is, None,
+                                    flags=ops.PRO_SILU_MUL))
+        elif self.ns:
             s = self.experts[-1]
             Is = self.I * self.ns
             A_f16 = x if s.q_gu.a_bits >= 16 else None
@@ -181,10 +206,27 @@ class MoELayer:
         T = x.shape[0]
         assert T <= self.max_tokens and self.EL == self.E, "use forward_rows for an expert-parallel shard"
         h = self.h
-        offs, src, slot = h.permute(topk_ids, self.E)
-        self.offs.copy_(offs)
+        _, src, slot = h.permute(topk_ids, self.E, self.offs, self.src[:T * self.topk], self.slot[:T])
         self.run_experts(x, src, T * self.topk, T)
         return h.combine(self.dn_out, slot, topk_w, self.s_dn if self.ns else None, out)
+
+    def capture(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: torch.Tensor):
+        """CUDA-graph one step over FIXED buffers and return the graph (`g.replay()` re-runs it on new contents).
+        A decode step (a few dozen tokens) is a chain of ~8 short launches: issued one by one it is bound by the host's
+        launch rate, as a graph by the kernels.  Nothing in forward() synchronises or depends on host values (row counts
+        stay on the device), so the capture is exact; two eager steps first fill the plan and table caches so that no
+        upload happens while capturing."""
+        side = torch.cuda.Stream(self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self.forward(x, topk_ids, topk_w, out)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            self.forward(x, topk_ids, topk_w, out)
+        return g
 
     def run_experts(self, x: torch.Tensor, src_row: Optional[torch.Tensor], n_rows: int, T_shared: int):
         """Rows already grouped by local expert (self.offs filled): quant -> gate_up -> silu*mul(+had)+quant -> down.
@@ -192,6 +234,10 @@ class MoELayer:
         (routed rows) and self.s_dn (shared expert over the first T_shared rows of x)."""
         h = self.h
         self._finalize_problems(T_shared, x)
+        if self.stream_fused:  # gather and silu*mul live in the GEMM kernel's row staging
+            h.group_gemm(self._gu_arr)
+            h.group_gemm(self._dn_arr)
+            return
         if True:
             h.quant_act(x, src_row, n_rows, self.offs, self.actq_gu(), False, self.x_q8, self.x_f16, self.x_sc)
         if self.ns:
@@ -237,6 +283,8 @@ class MoELayer:
 
     def launches_per_step(self) -> int:
         # permute (2) + act-quant (1 [+1 shared]) + GroupGEMM (1) + silu*mul+quant (1 [+1 shared]) + GroupGEMM (1) + combine (1)
+        if self.stream_fused:
+            return 5  # permute (2) + GroupGEMM (gather fused) + GroupGEMM (silu*mul fused) + combine
         n = 7 + (2 if self.ns else 0)
         if self.fused_silu:
             n -= (1 if self.h_direct else 0) + (1 if self.ns and self.sh_direct else 0)
@@ -262,16 +310,18 @@ class HostPipeline:
     H2D and D2H.  `submit` returns at once; `join()` makes the current stream wait for every download issued so far.
     The reference has no such path (its bench generates inputs on the device, test.cu:877-915)."""
 
-    def __init__(self, layer, T: int, depth: int = 2):
+    def __init__(self, layer, T: int, depth: int = 2, graph: bool = False):
+        """graph=True: every slot's step is captured once (MoELayer.capture) and replayed — for launch-bound decode steps."""
         d = layer.dev
         self.layer = layer
+        self.graph = graph
         self.s_in, self.s_out = torch.cuda.Stream(d), torch.cuda.Stream(d)
         self.slots = []
         for _ in range(depth):
             self.slots.append(dict(
                 x=torch.empty(T, layer.H, dtype=torch.float16, device=d), ids=torch.empty(T, layer.topk, dtype=torch.int32, device=d),
                 w=torch.empty(T, layer.topk, dtype=torch.float32, device=d), out=torch.empty(T, layer.H, dtype=torch.float16, device=d),
-                up=torch.cuda.Event(), done=torch.cuda.Event(), down=torch.cuda.Event()))
+                up=torch.cuda.Event(), done=torch.cuda.Event(), down=torch.cuda.Event(), g=None, T=None))
         self.n = 0
 
     def submit(self, x_host: torch.Tensor, ids_host: torch.Tensor, w_host: torch.Tensor, out_host: torch.Tensor):
@@ -287,7 +337,12 @@ class HostPipeline:
             sl["up"].record(self.s_in)
         cur.wait_event(sl["up"])
         cur.wait_event(sl["down"])        # the previous download of this slot's output is finished
-        self.layer.forward(sl["x"][:T], sl["ids"][:T], sl["w"][:T], sl["out"][:T])
+        if self.graph:
+            if sl["g"] is None or sl["T"] != T:
+                sl["g"], sl["T"] = self.layer.capture(sl["x"][:T], sl["ids"][:T], sl["w"][:T], sl["out"][:T]), T
+            sl["g"].replay()
+        else:
+            self.layer.forward(sl["x"][:T], sl["ids"][:T], sl["w"][:T], sl["out"][:T])
         sl["done"].record(cur)
         self.s_out.wait_event(sl["done"])
         with torch.cuda.stream(self.s_out):

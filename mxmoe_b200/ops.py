@@ -22,6 +22,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "lib
 
 
 EPI_SILU_MUL = 1  # MXB_EPI_SILU_MUL
+PRO_SILU_MUL = 2  # MXB_PRO_SILU_MUL
 
 
 class MxbError(RuntimeError):
@@ -36,7 +37,7 @@ class MxbProblem(C.Structure):
         ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
         ("a_bits", C.c_int32), ("w_bits", C.c_int32), ("gsize", C.c_int32), ("sym", C.c_int32),
         ("tile_n", C.c_int32), ("flags", C.c_int32),
-        ("c_row", C.c_void_p),
+        ("c_row", C.c_void_p), ("a_rows", C.c_void_p),
     ]
 
 
@@ -130,11 +131,12 @@ class Problem:
     tile_n: int = 0
     flags: int = 0  # EPI_SILU_MUL: B rows interleaved (gate_i, up_i), C = silu(gate)*up [M, N/2]
     c_row: Optional[torch.Tensor] = None  # device int32: first row of the problem in C when it is not m_range[0]
+    a_rows: Optional[torch.Tensor] = None  # device int32 per sorted row: the row of A to read (streaming path)
 
     def to_c(self) -> MxbProblem:
         return MxbProblem(_ptr(self.A), _ptr(self.B), _ptr(self.scale_a), _ptr(self.scale_b), _ptr(self.C),
                           _ptr(self.m_range), self.lda, self.ldc, self.M, self.N, self.K, self.a_bits, self.w_bits,
-                          self.gsize, 1 if self.sym else 0, self.tile_n, self.flags, _ptr(self.c_row))
+                          self.gsize, 1 if self.sym else 0, self.tile_n, self.flags, _ptr(self.c_row), _ptr(self.a_rows))
 
 
 class Handle:
@@ -241,13 +243,14 @@ class Handle:
         return list(out)
 
     # ---------------------------------------------------------------- MoE pieces
-    def permute(self, topk_ids: torch.Tensor, E: int):
+    def permute(self, topk_ids: torch.Tensor, E: int, offs=None, src=None, slot=None):
+        """offs / src / slot: optional preallocated outputs (int32 [E+1], [>= T*k], [>= T, k])"""
         T, k = topk_ids.shape
         dev = topk_ids.device
         ids = topk_ids.to(torch.int32).contiguous()
-        offs = torch.empty(E + 1, dtype=torch.int32, device=dev)
-        src = torch.empty(T * k, dtype=torch.int32, device=dev)
-        slot = torch.empty(T, k, dtype=torch.int32, device=dev)
+        offs = torch.empty(E + 1, dtype=torch.int32, device=dev) if offs is None else offs
+        src = torch.empty(T * k, dtype=torch.int32, device=dev) if src is None else src
+        slot = torch.empty(T, k, dtype=torch.int32, device=dev) if slot is None else slot
         self._check(self.lib.mxb_permute(self.h, _ptr(ids), T, k, E, _ptr(offs), _ptr(src), _ptr(slot), _stream()),
                     "mxb_permute")
         return offs, src, slot

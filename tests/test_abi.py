@@ -41,7 +41,7 @@ def test_ctypes_mirror_matches_header(lib):
     from mxmoe_b200 import ops
     names = sorted(n for n, _, _ in ops.EXPORTS)
     assert names == declared_symbols()
-    assert ctypes.sizeof(ops.MxbProblem) == 6 * 8 + 2 * 8 + 9 * 4 + 4 + 8  # 6 pointers, 2 int64, 9 int32, padding, c_row
+    assert ctypes.sizeof(ops.MxbProblem) == 6 * 8 + 2 * 8 + 9 * 4 + 4 + 16  # 6 pointers, 2 int64, 9 int32, padding, c_row, a_rows
     assert ctypes.sizeof(ops.MxbRowDest) == 32
     assert ctypes.sizeof(ops.MxbActQ) == 8
     assert ctypes.sizeof(ops.MxbTileChoice) == 24

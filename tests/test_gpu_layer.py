@@ -102,3 +102,61 @@ def test_fused_silu_epilogue_layer_is_bit_identical(hadamard):
     torch.cuda.synchronize()
     assert torch.isfinite(outs[0].float()).all()
     assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))
+
+
+@pytest.mark.parametrize("gsize,sym", [(128, False), (-1, True)])
+def test_decode_layer_stream_fused_is_bit_identical_and_graphable(gsize, sym):
+    """Decode step of a weight-only 4-bit layer (the c3 shape scaled down, 24 tokens, one expert left empty, a shared
+    expert with ns = 2): the streaming kernel with the token gather (MxbProblem.a_rows) and act_fn(gate)*up
+    (MXB_PRO_SILU_MUL) folded into its row staging against (a) the same layer run as separate
+    quant_act / GroupGEMM / silu_mul_quant / GroupGEMM launches: identical bits; (b) the oracle within the w4a16
+    tolerance; (c) its own CUDA-graph replay on new inputs: identical bits."""
+    from mxmoe_b200 import ops
+    from mxmoe_b200.config import qmodel_cfg_from_dict
+    from mxmoe_b200.layer import MoELayer
+    E, k, Hd, I, ns, T = 8, 3, 256, 384, 2, 24
+    c = lin(4, 16, gsize, sym)
+    ex = {str(e): {"gate": dict(c), "up": dict(c), "down": dict(c)} for e in range(E + 1)}
+    ql = qmodel_cfg_from_dict({"0": {"experts": ex}}).layers["0"]
+    rng = np.random.default_rng(11)
+    weights = {}
+    for e in range(E + 1):
+        Ie = I * ns if e == E else I
+        weights[e] = (((rng.random((2 * Ie, Hd)) * 2 - 1) * (2.0 / np.sqrt(Hd))).astype(np.float16),
+                      ((rng.random((Hd, Ie)) * 2 - 1) * (2.0 / np.sqrt(Ie))).astype(np.float16))
+    tw = {e: (torch.from_numpy(a), torch.from_numpy(b)) for e, (a, b) in weights.items()}
+
+    def inputs(seed):
+        r = np.random.default_rng(seed)
+        x = (r.random((T, Hd)) * 2 - 1).astype(np.float16)
+        ids = np.stack([r.permutation(E - 1)[:k] for _ in range(T)]).astype(np.int32)  # expert E-1 never routed to
+        w = r.random((T, k)).astype(np.float32)
+        return x, ids, w / w.sum(1, keepdims=True)
+
+    x, ids, w = inputs(0)
+    dx, dids, dw = torch.from_numpy(x).cuda(), torch.from_numpy(ids).cuda(), torch.from_numpy(w).cuda()
+    h = ops.Handle(0)
+    fused = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw)
+    assert fused.stream_fused and fused.launches_per_step() == 5
+    plain = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw)
+    plain.stream_fused = False
+    plain._build_problems()
+    y_f = fused.forward(dx, dids, dw).clone()
+    y_p = plain.forward(dx, dids, dw).clone()
+    torch.cuda.synchronize()
+    assert torch.isfinite(y_f.float()).all()
+    assert torch.equal(y_f.view(torch.int16), y_p.view(torch.int16))
+    qc = [((4, 16, gsize, sym), (4, 16, gsize, sym))] * (E + 1)
+    ref = O.moe_layer(x, ids, w, weights, qc, E, False, (weights[E][0], weights[E][1], qc[E][0], qc[E][1]))
+    o, r = y_f.cpu().numpy().astype(np.float64), ref.astype(np.float64)
+    assert np.abs(o - r).max() <= 2e-3 * np.abs(r).max()
+    # CUDA graph over fixed buffers, replayed on new contents
+    out = torch.empty_like(y_f)
+    g = fused.capture(dx, dids, dw, out)
+    x2, ids2, w2 = inputs(1)
+    dx.copy_(torch.from_numpy(x2)); dids.copy_(torch.from_numpy(ids2)); dw.copy_(torch.from_numpy(w2))
+    g.replay()
+    torch.cuda.synchronize()
+    y2 = fused.forward(dx, dids, dw)
+    torch.cuda.synchronize()
+    assert torch.equal(out.view(torch.int16), y2.view(torch.int16))
