@@ -201,6 +201,158 @@ __global__ void __launch_bounds__(256) hadamard_quant_kernel(HadParams p) {
 }
 
 
+// ---------------------------------------------------------------------------------------------------------
+// Long rows (power-of-two part m > 128, e.g. the fused shared expert of Qwen2-57B: n = 20480 = 40 x 512): one CTA of
+// 16 warps per row instead of one warp.  hadamard_quant_kernel above keeps a whole row per WARP in shared memory
+// (4n bytes), which leaves two warps per SM at this length (measured 5.06 ms for 8192 x 20480, 58 % of the c5 step).
+// Same arithmetic, step for step (butterfly network and order, fp16 staging, the same m16n8k16 tiles in the same k
+// order, quant8), so the two kernels agree bit for bit; only the work distribution differs.
+template <bool SILU>
+__global__ void __launch_bounds__(512, 2) hadamard_wide_kernel(HadParams p) {
+  extern __shared__ __align__(16) uint8_t hsm[];
+  __shared__ float red[16];
+  if (p.E > 1 && p.expert_offsets != nullptr) p.n_rows = min(p.n_rows, p.expert_offsets[p.E]);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int hbytes = p.Kp * p.h_pitch;
+  {
+    const int chunks_per_row = p.Kp / 8;
+    for (int i = tid; i < p.Kp * chunks_per_row; i += 512) {
+      const int r = i / chunks_per_row, c = i % chunks_per_row;
+      *reinterpret_cast<uint4*>(hsm + r * p.h_pitch + c * 16) = *reinterpret_cast<const uint4*>(p.hmat + r * p.Kp + c * 8);
+    }
+  }
+  uint8_t* wbuf = hsm + hbytes;
+  float* F = reinterpret_cast<float*>(wbuf);
+  __half* Xh = reinterpret_cast<__half*>(wbuf);
+  const int n = p.n, n8 = n >> 3, m = p.m;
+  __half* Yh = Xh + p.Kp * m;
+  __syncthreads();
+
+  for (int row = blockIdx.x; row < p.n_rows; row += gridDim.x) {
+    int a_bits = p.actq[0].x;
+    if (p.E > 1) a_bits = p.actq[find_expert(p.expert_offsets, p.E, row)].x;
+    const int64_t srow = p.src_row ? p.src_row[row] : row;
+    const __half* in = p.x + srow * p.in_pitch;
+    // ---- load (+ silu*mul), butterflies of stride 1,2,4 in registers, stage as fp32
+    for (int i = tid; i < n8; i += 512) {
+      float v[8];
+      load8<SILU>(in, n, i, v);
+#pragma unroll
+      for (int h = 1; h < 8; h <<= 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if ((j & h) == 0) {
+            const float a = v[j], b = v[j + h];
+            v[j] = a + b;
+            v[j + h] = a - b;
+          }
+        }
+      }
+      *reinterpret_cast<float4*>(F + i * 8) = make_float4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<float4*>(F + i * 8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    __syncthreads();
+    // ---- remaining butterflies in shared memory
+    for (int h = 8; h < m; h <<= 1) {
+      for (int t = tid; t < n / 2; t += 512) {
+        const int i = ((t / h) * 2 * h) + (t % h);
+        const float a = F[i], b = F[i + h];
+        F[i] = a + b;
+        F[i + h] = a - b;
+      }
+      __syncthreads();
+    }
+    // ---- scale by 1/sqrt(n), round to fp16, convert in place: a round's fp16 bytes land on fp32 bytes of this or
+    // earlier rounds only, and every round reads before it writes
+    for (int i0 = 0; i0 < n8; i0 += 512) {
+      const int i = i0 + tid;
+      uint4 pk = make_uint4(0, 0, 0, 0);
+      if (i < n8) {
+        const float4 a = *reinterpret_cast<const float4*>(F + i * 8);
+        const float4 b = *reinterpret_cast<const float4*>(F + i * 8 + 4);
+        __half2* ph = reinterpret_cast<__half2*>(&pk);
+        ph[0] = __floats2half2_rn(a.x * p.scale, a.y * p.scale);
+        ph[1] = __floats2half2_rn(a.z * p.scale, a.w * p.scale);
+        ph[2] = __floats2half2_rn(b.x * p.scale, b.y * p.scale);
+        ph[3] = __floats2half2_rn(b.z * p.scale, b.w * p.scale);
+      }
+      __syncthreads();
+      if (i < n8) *reinterpret_cast<uint4*>(Xh + i * 8) = pk;
+    }
+    // zero the padding rows K..Kp-1 of the B operand (past the converted data; the fp32 copy is dead)
+    for (int i = n + tid * 8; i < p.Kp * m; i += 512 * 8) *reinterpret_cast<uint4*>(Xh + i) = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+    // ---- Y[K, m] = hadK[K, K] @ X[K, m]: (16-row, 32-column) tile groups dealt to the 16 warps
+    {
+      const int mt_n = p.Kp / 16, nt_n = m / 8, kt_n = p.Kp / 16, ngrp = (nt_n + 3) / 4;
+      const uint32_t hs = s_u32(hsm), xs = s_u32(Xh);
+      for (int g = warp; g < mt_n * ngrp; g += 16) {
+        const int mt = g / ngrp, nc = (g - mt * ngrp) * 4;
+        float acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+        for (int kt = 0; kt < kt_n; ++kt) {
+          uint32_t af[4];
+          ldsm_x4(hs + (mt * 16 + (lane & 15)) * p.h_pitch + (kt * 16 + (lane >> 4) * 8) * 2, af);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (nc + q < nt_n) {
+              uint32_t bf[2];
+              ldsm_x2_trans(xs + ((kt * 16 + (lane & 15)) * m + (nc + q) * 8) * 2, bf);
+              mma_16816(acc[q], af, bf);
+            }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (nc + q < nt_n) {
+            const int r0 = mt * 16 + (lane >> 2), c0 = (nc + q) * 8 + (lane & 3) * 2;
+            if (r0 < p.K) *reinterpret_cast<__half2*>(Yh + r0 * m + c0) = __floats2half2_rn(acc[q][0], acc[q][1]);
+            if (r0 + 8 < p.K) *reinterpret_cast<__half2*>(Yh + (r0 + 8) * m + c0) = __floats2half2_rn(acc[q][2], acc[q][3]);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- per-token quantization straight from shared memory (per-token scale: gsize -1)
+    if (a_bits >= 16) {
+      __half* o = p.out_f16 + static_cast<int64_t>(row) * n;
+      for (int i = tid; i < n8; i += 512) *reinterpret_cast<uint4*>(o + i * 8) = *reinterpret_cast<const uint4*>(Yh + i * 8);
+    } else {
+      const int iupper = (1 << (a_bits - 1)) - 1;
+      float amax = 0.f;
+      for (int i = tid; i < n8; i += 512) {
+        const uint4 u = *reinterpret_cast<const uint4*>(Yh + i * 8);
+        const __half* uh = reinterpret_cast<const __half*>(&u);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fabsf(__half2float(uh[j])));
+      }
+      amax = warp_max(amax);
+      if (lane == 0) red[warp] = amax;
+      __syncthreads();
+      amax = red[0];
+#pragma unroll
+      for (int w = 1; w < 16; ++w) amax = fmaxf(amax, red[w]);
+      const __half sh = make_scale(amax, static_cast<float>(iupper));
+      const float sf = __half2float(sh), rcp = __frcp_rn(sf);
+      if (tid == 0) p.scales[static_cast<int64_t>(row) * p.scale_cols] = sh;
+      int8_t* o = p.out_q8 + static_cast<int64_t>(row) * n;
+      for (int i = tid; i < n8; i += 512) {
+        const uint4 u = *reinterpret_cast<const uint4*>(Yh + i * 8);
+        const __half* uh = reinterpret_cast<const __half*>(&u);
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __half2float(uh[j]);
+        *reinterpret_cast<uint2*>(o + i * 8) = quant8(v, sf, rcp, iupper);
+      }
+    }
+    __syncthreads();  // the staging is reused by the next row
+  }
+}
+
+
 #include "hadamard_mma.inc"
 #include "hadamard_umma.inc"
 
@@ -263,6 +415,24 @@ cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t
   wb = (wb + 15) & ~15;
   p.warp_bytes = wb;
   const int hbytes = K > 1 ? Kp * p.h_pitch : 0;
+  // long rows: one CTA per row (hadamard_wide_kernel); MXB_HAD_WIDE=0 keeps the warp-per-row kernel (tests compare the two)
+  const char* wide_env = getenv("MXB_HAD_WIDE");
+  if ((!wide_env || atoi(wide_env) != 0) && K > 1 && p.m > 128 && !any_g128 && hbytes + wb <= 226 * 1024) {
+    const int smem = hbytes + wb;
+    int grid = sm_count * (2 * (smem + 1024) <= 227 * 1024 ? 2 : 1);
+    if (grid > n_rows) grid = n_rows;
+    cudaError_t e;
+    if (silu) {
+      e = cudaFuncSetAttribute(hadamard_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);  // + 64 B static
+      if (e != cudaSuccess) return e;
+      hadamard_wide_kernel<true><<<grid, 512, smem, st>>>(p);
+    } else {
+      e = cudaFuncSetAttribute(hadamard_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+      if (e != cudaSuccess) return e;
+      hadamard_wide_kernel<false><<<grid, 512, smem, st>>>(p);
+    }
+    return cudaGetLastError();
+  }
   const int budget = 227 * 1024 - hbytes;
   int warps = budget / wb;
   if (warps < 1) return cudaErrorInvalidValue;

@@ -132,6 +132,40 @@ def test_hadamard_silu_quant_close_to_oracle(H):
     assert np.mean(q8.cpu().numpy().astype(np.int32) != rq) < 0.02
 
 
+@pytest.mark.parametrize("n,silu,bits", [(20480, False, 8), (10240, True, 4), (20480, True, 16), (7168, False, 8)])
+def test_hadamard_long_rows_cta_per_row_kernel(H, n, silu, bits, monkeypatch):
+    """Rows whose power-of-two part exceeds 128 (Qwen2-57B's fused shared expert: 20480 = 40 x 512; 7168 = 28 x 256)
+    take hadamard_wide_kernel (one CTA per row): against the oracle, and bit for bit against the warp-per-row kernel
+    it replaces (MXB_HAD_WIDE=0) -- same butterfly network, same fp16 staging, same MMA tiles, same quant8."""
+    rng = np.random.default_rng(n + bits)
+    rows = 21
+    x = rand16(rng, rows, 2 * n if silu else n, scale=2.0)
+    x[2, 5] = 30.0
+    actq = [(bits, -1)]
+
+    def run():
+        if silu:
+            return H.silu_mul_quant(dev(x), rows, None, actq, hadamard=True)
+        return H.quant_act(dev(x), None, rows, None, actq, hadamard=True)
+    q8, f16, sc = run()
+    torch.cuda.synchronize()
+    monkeypatch.setenv("MXB_HAD_WIDE", "0")
+    q8b, f16b, scb = run()
+    torch.cuda.synchronize()
+    monkeypatch.delenv("MXB_HAD_WIDE")
+    h = O.hadamard_f16(O.silu_mul(x) if silu else x)
+    if bits == 16:
+        assert torch.equal(f16.view(torch.int16), f16b.view(torch.int16))
+        got, ref = f16.cpu().numpy().astype(np.float64), h.astype(np.float64)
+        assert np.abs(got - ref).max() <= 2e-3 * np.abs(ref).max()
+    else:
+        assert torch.equal(q8, q8b) and torch.equal(sc.view(torch.int16), scb.view(torch.int16))
+        rq, rs = O.quant_act(h, bits, -1)
+        deq = q8.cpu().numpy().astype(np.float32) * sc.cpu().numpy().astype(np.float32)
+        assert np.abs(deq - rq.astype(np.float32) * rs.astype(np.float32)).max() <= 1.01 * rs.astype(np.float32).max()
+        assert np.mean(q8.cpu().numpy().astype(np.int32) != rq) < 0.02
+
+
 def test_combine_bit_exact(H):
     rng = np.random.default_rng(4)
     T, k, E, Hd = 333, 4, 12, 2048
