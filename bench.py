@@ -31,6 +31,9 @@ WORKLOADS = {
                name="DeepSeek-V2-Lite MoE layer w4a16_g128 weight-only bs=64"),
     "c4": dict(model="mixtral", layer=0, bs=8192, q="w8a8_g-1_sym", hadamard=False,
                name="Mixtral-8x7B MoE layer w8a8_g-1_sym bs=8192"),
+    # the reference's FP8 kind (tile_config.py:45) on the c4 shape: tcgen05.mma kind::f8f6f4
+    "c4_e4m3": dict(model="mixtral", layer=0, bs=8192, q="w8a8_g-1_sym_E4M3", hadamard=False,
+                    name="Mixtral-8x7B MoE layer w8a8_g-1_sym_E4M3 bs=8192"),
     "c5": dict(model="qwen2_moe_57b", layer=0, bs=8192, q="mixed5", hadamard=True,
                name="Qwen2-57B-A14B MoE layer mixed w4a4+w8a8 bs=8192"),
 }
@@ -318,7 +321,8 @@ def main():
 
     line = {"metric": "MoE-layer GroupGEMM TOPS", "value": value, "unit": "TOPS", "n_gpus": W, "steps": steps, "warmup": warmup,
             "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int8 tensor cores over int4/int8 grids, fp16 out" if roof["bound"] == "tensor" else "fp16", "data": "synthetic",
+            "dtype": ("fp8 (E4M3) tensor cores, fp32 accumulate, fp16 out" if "E4M3" in wl["q"] else
+                      "int8 tensor cores over int4/int8 grids, fp16 out") if roof["bound"] == "tensor" else "fp16", "data": "synthetic",
             "config": cfg, "clocks": sampler.result(), "e2e": e2e, "gpu_launches": layer.launches_per_step() * steps,
             "roofline": roof}
     if rank == 0:

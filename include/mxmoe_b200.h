@@ -45,6 +45,7 @@ typedef struct mxb_context* mxb_handle_t;
  * Operand formats ("native" layouts, produced by mxb_quant_pack_weight / mxb_repack_from_ref / mxb_quant_act):
  *   fp16      (w16 a16) : A fp16 [M,K] (row pitch lda elements), B fp16 [N,K]
  *   w8a8      sym g-1   : A int8 [M,K], B int8 [N,K], scale_a fp16 [M], scale_b fp16 [N]
+ *   w8a8 E4M3 sym g-1   : a_bits = w_bits = MXB_BITS_E4M3: same shapes, bytes are E4M3 codes
  *   w4a4      sym g-1   : A int8 containers holding values in [-7,7] [M,K]; B 4-bit [N,K/2] bytes, inside
  *                         every 32-k block byte j holds k=j in the low and k=j+16 in the high nibble
  *                         (two's complement); scale_a fp16 [M], scale_b fp16 [N]
@@ -60,6 +61,13 @@ typedef struct mxb_context* mxb_handle_t;
  * of buffers shared by all problems and this problem owns rows [row_begin,row_end); M is the row capacity
  * of those buffers.
  */
+/* Bit-width code of 8-bit floating-point containers (E4M3: 4 exponent bits, 3 mantissa bits, max 448, no infinities):
+ * the reference's `w8a8_g-1_sym_E4M3` (mxmoe/kernels/tile_config.py:45,105 MMA_E4M3_K32).  Wherever a_bits / w_bits
+ * is taken, this value selects E4M3 instead of int8: per-token / per-channel scale = absmax / 448, codes rounded to
+ * nearest even; the GEMM runs tcgen05.mma kind::f8f6f4 with fp32 accumulation and the int path's scale order
+ * (acc * half(sa * sb)).  Both operands must be E4M3, scales per token and per channel (gsize -1). */
+#define MXB_BITS_E4M3 (-8)
+
 typedef struct MxbProblem {
   const void* A;
   const void* B;

@@ -14,6 +14,9 @@ import re
 from typing import Dict, List, Optional, Tuple
 
 
+BITS_E4M3 = -8  # MXB_BITS_E4M3 (include/mxmoe_b200.h): 8-bit E4M3 containers
+
+
 @dataclasses.dataclass
 class QLinearConfig:
     w_bits: int = 16
@@ -26,11 +29,13 @@ class QLinearConfig:
     a_clip: Tuple[float, float] = (1.0, 1.0)
 
     def __str__(self):
-        return f"W{self.w_bits}A{self.a_bits}_g{self.w_gsize}_{'sym' if self.w_sym else 'asym'}"
+        return self.qstr().upper() if self.w_bits == BITS_E4M3 else f"W{self.w_bits}A{self.a_bits}_g{self.w_gsize}_{'sym' if self.w_sym else 'asym'}"
 
     def qstr(self) -> str:
         if self.w_bits == 16 and self.a_bits == 16:
             return "fp16"
+        if self.w_bits == BITS_E4M3:  # the reference's name for the FP8 kind (tile_config.py:45)
+            return f"w8a8_g{self.w_gsize}_sym_E4M3"
         return f"w{self.w_bits}a{self.a_bits}_g{self.w_gsize}_{'sym' if self.w_sym else 'asym'}"
 
     def to_dict(self) -> dict:
@@ -46,10 +51,14 @@ class QLinearConfig:
         """`w4a16_g128_asym` -> config; None / 'fp16' -> 16/16 (parsing of gen_workload.py:48-60)."""
         if qstr is None or qstr == "fp16":
             return QLinearConfig(16, -1, True, (1.0, 1.0), 16, -1, True, (1.0, 1.0))
-        m = re.fullmatch(r"w(\d+)a(\d+)_g(-?\d+)_(sym|asym)", qstr)
+        m = re.fullmatch(r"w(\d+)a(\d+)_g(-?\d+)_(sym|asym)(_E4M3)?", qstr)
         if not m:
             raise ValueError(f"bad qstr {qstr!r}")
         w, a, g = int(m.group(1)), int(m.group(2)), int(m.group(3))
+        if m.group(5):  # 8-bit float containers: bit-width code MXB_BITS_E4M3 for both operands
+            if (w, a, g, m.group(4)) != (8, 8, -1, "sym"):
+                raise ValueError(f"bad qstr {qstr!r}: the E4M3 kind is w8a8_g-1_sym_E4M3")
+            w = a = BITS_E4M3
         return QLinearConfig(w, g, m.group(4) == "sym", (1.0, 1.0), a, g, True, (1.0, 1.0))
 
 

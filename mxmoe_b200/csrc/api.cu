@@ -124,6 +124,7 @@ struct KindInfo {
 int classify(const MxbProblem& p, KindInfo* k) {
   const int w = p.w_bits, a = p.a_bits, g = p.gsize;
   if (g != -1 && g != 128) return fail(MXB_EINVAL, "quant type not supported: gsize %d (only -1 or 128)", g);
+  if ((a == MXB_BITS_E4M3) != (w == MXB_BITS_E4M3)) return fail(MXB_EINVAL, "quant type not supported: E4M3 needs both operands in E4M3");
   if (w == 16 && a == 16) {
     *k = {mxb::MMA_F16, mxb::CONV_NONE, mxb::EPI_F32, 0, 2, 64, 128};
     return MXB_OK;
@@ -134,6 +135,10 @@ int classify(const MxbProblem& p, KindInfo* k) {
   }
   if (a == 8 && w == 8 && p.sym) {
     *k = {mxb::MMA_I8, mxb::CONV_NONE, g == -1 ? mxb::EPI_INT_ROWCOL : mxb::EPI_INT_GROUP, 0, 1, 128, 128};
+    return MXB_OK;
+  }
+  if (a == MXB_BITS_E4M3 && w == MXB_BITS_E4M3 && p.sym && g == -1) {  // w8a8_g-1_sym_E4M3 (tile_config.py:45,105): kind::f8f6f4
+    *k = {mxb::MMA_F8, mxb::CONV_NONE, mxb::EPI_INT_ROWCOL, 0, 1, 128, 128};
     return MXB_OK;
   }
   if (a == 4 && w == 4 && p.sym) {
@@ -554,8 +559,10 @@ int actq_table(mxb_context* c, const MxbActQ* actq, int E, cudaStream_t st, cons
   *any_g128 = *any_q = *any_f16 = 0;
   for (int e = 0; e < E; ++e) {
     const int a = actq[e].a_bits, g = actq[e].gsize;
-    if (!(a == 16 || a == 8 || a == 4)) return fail(MXB_EINVAL, "expert %d: a_bits %d not supported (16, 8, 4)", e, a);
+    if (!(a == 16 || a == 8 || a == 4 || a == MXB_BITS_E4M3))
+      return fail(MXB_EINVAL, "expert %d: a_bits %d not supported (16, 8, 4, MXB_BITS_E4M3)", e, a);
     if (a != 16 && g != -1 && g != 128) return fail(MXB_EINVAL, "expert %d: activation gsize %d not supported (-1, 128)", e, g);
+    if (a == MXB_BITS_E4M3 && g != -1) return fail(MXB_EINVAL, "expert %d: E4M3 activations take per-token scales only", e);
     if (a == 16) *any_f16 = 1; else *any_q = 1;
     if (a != 16 && g == 128) *any_g128 = 1;
   }
@@ -622,8 +629,11 @@ int quant_common(mxb_context* c, bool silu, const void* x, int H, const int32_t*
       rc = hadamard_matrix(c, K, &hmat, &Kp);
       if (rc) return rc;
     }
+    // group-wise and E4M3 quantization tails exist in the warp-per-row kernel only (quantize_row)
+    bool generic = g128 != 0;
+    for (int e = 0; e < E; ++e) generic = generic || actq[e].a_bits == MXB_BITS_E4M3;
     cudaError_t e = mxb::hadamard_quant_launch(silu, x, H, src_row, n_rows, expert_offsets, tab, E, out_q8, out_f16, scales,
-                                               scale_cols, hmat, K, Kp, c->sm_count, g128 != 0, st);
+                                               scale_cols, hmat, K, Kp, c->sm_count, generic, st);
     if (e != cudaSuccess) return fail(MXB_ECUDA, "hadamard_quant_launch: %s", cudaGetErrorString(e));
     return MXB_OK;
   }
@@ -668,6 +678,7 @@ void build_inv_table(int bits, std::vector<int32_t>* inv) {
 }
 
 int native_layout(int w_bits, int a_bits) {
+  if (w_bits == MXB_BITS_E4M3 || a_bits == MXB_BITS_E4M3) return (w_bits == a_bits) ? 4 : -1;
   if (a_bits < 16) return w_bits == 8 ? 0 : (w_bits == 4 ? 1 : -1);
   return w_bits == 4 ? 2 : (w_bits == 8 ? 3 : -1);
 }
@@ -774,7 +785,7 @@ int mxb_interleave_gate_up(mxb_handle_t c, const void* src, int I, int64_t row_b
   return MXB_OK;
 }
 
-int64_t mxb_packed_bytes(int N, int K, int w_bits) { return int64_t(N) * K * w_bits / 8; }
+int64_t mxb_packed_bytes(int N, int K, int w_bits) { return int64_t(N) * K * (w_bits < 0 ? -w_bits : w_bits) / 8; }
 
 int64_t mxb_scale_elems(int N, int K, int w_bits, int a_bits, int gsize, int sym) {
   (void)w_bits; (void)a_bits;
@@ -788,10 +799,11 @@ int mxb_quant_pack_weight(mxb_handle_t c, const void* W, int N, int K, int w_bit
   const int layout = native_layout(w_bits, a_bits);
   if (layout < 0) return fail(MXB_EINVAL, "quant type not supported: w%da%d", w_bits, a_bits);
   if (a_bits < 16 && !sym) return fail(MXB_EINVAL, "quant type not supported: asymmetric WxAx");
+  if (layout == 4 && gsize > 0) return fail(MXB_EINVAL, "quant type not supported: E4M3 weights take per-channel scales only");
   if (K % 32 != 0 || (gsize > 0 && K % gsize != 0) || K > 96 * 1024) return fail(MXB_EINVAL, "bad K=%d for gsize %d", K, gsize);
   if (!W || !packed || !scales) return fail(MXB_EINVAL, "null pointer");
   CU_OK(cudaSetDevice(c->device));
-  CU_OK(mxb::quant_pack_weight_launch(W, N, K, w_bits, gsize, sym, layout, packed, scales, static_cast<cudaStream_t>(stream)));
+  CU_OK(mxb::quant_pack_weight_launch(W, N, K, w_bits < 0 ? 8 : w_bits, gsize, sym, layout, packed, scales, static_cast<cudaStream_t>(stream)));
   return MXB_OK;
 }
 

@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
         const int kblocks = d.kblocks;
         const int kpg = d.epi == EPI_INT_GROUP ? d.kb_per_group : kblocks;
         const uint32_t idesc = d.idesc;
-        const bool is_i8 = d.mma_kind == MMA_I8;
+        const bool is_i8 = d.mma_kind == MMA_I8, is_f8 = d.mma_kind == MMA_F8;
         const bool has_conv = d.conv != CONV_NONE;
         for (int kb0 = 0; kb0 < kblocks; kb0 += kpg) {
           mbar_wait(&S.tmem_empty[acc], acc_phase ^ 1);
@@ -235,6 +235,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
             for (int k = 0; k < 4; ++k) {
               const uint32_t accum = (kb > kb0 || k > 0) ? 1u : 0u;
               if (is_i8) umma_i8(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+              else if (is_f8) umma_f8(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
               else       umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
             }
             umma_commit(&S.empty[stage]);
@@ -267,6 +268,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
       __half* C = d.C;
       const __half* sb = d.scale_b;
       const int shift = d.acc_shift;
+      const bool facc = d.mma_kind == MMA_F8;  // fp32 accumulators (kind::f8f6f4)
       const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
 
       if (epi != EPI_INT_GROUP) {
@@ -300,9 +302,9 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
               for (int j = 0; j < 4; ++j) {
                 __half2 prod = __hmul2(sa2, *reinterpret_cast<const __half2*>(&sw[j]));
                 float2 pf = __half22float2(prod);
-                int a0 = static_cast<int32_t>(v[g * 8 + 2 * j]) >> shift;
-                int a1 = static_cast<int32_t>(v[g * 8 + 2 * j + 1]) >> shift;
-                h[g * 4 + j] = pack_half2(__int2float_rn(a0) * pf.x, __int2float_rn(a1) * pf.y);
+                const float a0 = facc ? __uint_as_float(v[g * 8 + 2 * j]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j]) >> shift);
+                const float a1 = facc ? __uint_as_float(v[g * 8 + 2 * j + 1]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j + 1]) >> shift);
+                h[g * 4 + j] = pack_half2(a0 * pf.x, a1 * pf.y);
               }
             }
           }

@@ -12,7 +12,7 @@
 
 namespace mxb {
 
-enum MmaKind : int32_t { MMA_F16 = 0, MMA_I8 = 1 };
+enum MmaKind : int32_t { MMA_F16 = 0, MMA_I8 = 1, MMA_F8 = 2 };  // tcgen05.mma kind::f16 / kind::i8 / kind::f8f6f4 (E4M3 x E4M3)
 enum ConvMode : int32_t {
   CONV_NONE = 0,
   CONV_W4_I8 = 1,   // 4-bit two's complement weights -> int8 x16 (nibble split), w4a4

@@ -244,7 +244,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
         const int kblocks = d.kblocks;
         const int nt16 = (t.nt + 15) & ~15;
         const uint32_t idesc = d.idesc | ((uint32_t(nt16) >> 3) << 17);
-        const bool is_i8 = d.mma_kind == MMA_I8;
+        const bool is_i8 = d.mma_kind == MMA_I8, is_f8 = d.mma_kind == MMA_F8;
         const bool has_conv = d.conv != CONV_NONE;
         mbar_wait(&S.tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
@@ -264,6 +264,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
             for (int k = 0; k < 4; ++k) {
               const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
               if (is_i8) umma_i8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+              else if (is_f8) umma_f8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
               else       umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
             }
             umma_commit_pair(&S.empty[stage], 3);
@@ -296,6 +297,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       const int shift = d.acc_shift;
       const int64_t ldc = d.ldc;
       const bool silu = (d.epi_flags & 1) != 0;
+      const bool facc = d.mma_kind == MMA_F8;
       const int grow0 = S.row0[t.p] + t.t0;  // global row of the tile's first token
       // C may start at another row than A (DevProblem::c_row): results written straight into a peer GPU's buffer
       const int crow0 = (d.c_row != nullptr ? __ldg(d.c_row) : S.row0[t.p]) + t.t0;
@@ -338,9 +340,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
             for (int j = 0; j < 4; ++j) {
               const __half2 prod = __hmul2(*reinterpret_cast<const __half2*>(&sw[j]), sb2);
               const float2 pf = __half22float2(prod);
-              const int a0 = static_cast<int32_t>(v[g * 8 + 2 * j]) >> shift;
-              const int a1 = static_cast<int32_t>(v[g * 8 + 2 * j + 1]) >> shift;
-              h[g * 4 + j] = pack_half2(__int2float_rn(a0) * pf.x, __int2float_rn(a1) * pf.y);
+              // integer accumulators (>> shift: the x16 of the in-smem w4 expansion) or fp32 ones (kind::f8f6f4)
+              const float a0 = facc ? __uint_as_float(v[g * 8 + 2 * j]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j]) >> shift);
+              const float a1 = facc ? __uint_as_float(v[g * 8 + 2 * j + 1]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j + 1]) >> shift);
+              h[g * 4 + j] = pack_half2(a0 * pf.x, a1 * pf.y);
             }
           }
         }

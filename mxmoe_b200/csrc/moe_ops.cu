@@ -334,6 +334,7 @@ namespace {
 //   layout 1: 4-bit two's complement, 32-k blocks, byte j = k j (low nibble) | k j+16 (high)   (w4a4)
 //   layout 2: unsigned 4-bit codes, nibble order 0,2,4,6,1,3,5,7 inside each 32-bit word       (w4a16)
 //   layout 3: unsigned 8-bit codes [N,K]                                                      (w8a16)
+//   layout 4: E4M3 bytes [N,K], per-channel scale absmax / 448                                  (w8a8 E4M3)
 __global__ void __launch_bounds__(256) quant_pack_weight_kernel(const __half* __restrict__ W, int N, int K, int bits, int gsize,
                                                                  int sym, int layout, uint8_t* __restrict__ packed,
                                                                  __half* __restrict__ scales) {
@@ -343,7 +344,8 @@ __global__ void __launch_bounds__(256) quant_pack_weight_kernel(const __half* __
   const int G = K / g;
   const __half* w = W + static_cast<int64_t>(n) * K;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const float upper = sym ? static_cast<float>((1 << (bits - 1)) - 1) : static_cast<float>((1 << bits) - 1);
+  const bool e4m3 = layout == 4;  // 8-bit float codes: scale = absmax / 448, q = e4m3(w / scale), round to nearest even
+  const float upper = e4m3 ? 448.f : (sym ? static_cast<float>((1 << (bits - 1)) - 1) : static_cast<float>((1 << bits) - 1));
   const float lower = sym ? -upper : 0.f;
   for (int gi = warp; gi < G; gi += 8) {
     float mx = -65504.f, mn = 65504.f, amx = 0.f;
@@ -370,16 +372,20 @@ __global__ void __launch_bounds__(256) quant_pack_weight_kernel(const __half* __
         scales[(static_cast<int64_t>(gi) * N + n) * 2 + 1] = __float2half_rn(zp);
       }
     }
-    const int bias = (layout >= 2 && sym) ? (1 << (bits - 1)) - 1 : 0;
+    const int bias = ((layout == 2 || layout == 3) && sym) ? (1 << (bits - 1)) - 1 : 0;
     for (int i = lane; i < g; i += 32) {
       float v = __half2float(w[gi * g + i]);
+      if (e4m3) {
+        codes[gi * g + i] = static_cast<uint8_t>(__nv_cvt_float_to_fp8(__fdiv_rn(v, sf), __NV_SATFINITE, __NV_E4M3));
+        continue;
+      }
       float q = h_round(__fdiv_rn(h_round(v - zp), sf));
       q = rintf(fminf(fmaxf(q, lower), upper));
       codes[gi * g + i] = static_cast<uint8_t>(static_cast<int>(q) + bias);
     }
   }
   __syncthreads();
-  if (layout == 0 || layout == 3) {
+  if (layout == 0 || layout == 3 || layout == 4) {
     uint8_t* o = packed + static_cast<int64_t>(n) * K;
     for (int i = threadIdx.x; i < K; i += 256) o[i] = codes[i];
   } else if (layout == 1) {

@@ -3,11 +3,15 @@
 // operation rounded to fp16 the way torch does for half tensors, plus the scale==0 -> 1 guard of the
 // reference kernel (mxmoe/kernels/src/include/quantize.cuh:256).
 #pragma once
+#include <cuda_fp8.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace mxb {
+
+constexpr int kBitsE4M3 = -8;  // MXB_BITS_E4M3: bit-width code of 8-bit E4M3 containers (include/mxmoe_b200.h)
+
 
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
@@ -81,6 +85,21 @@ __device__ __forceinline__ uint2 quant8(const float (&v)[8], float sf, float rcp
   pk.y = __byte_perm(w[2], w[3], 0x6420);
   return pk;
 }
+// 8 quotients -> 8 E4M3 bytes (round to nearest even, saturating at +-448): the fp8 counterpart of quant8.  The E4M3
+// rounding boundaries are fp16-representable, so the argument above carries over: e4m3(q1) == e4m3(x / s) always.
+__device__ __forceinline__ uint2 quant8_e4m3(const float (&v)[8], float sf, float rcp) {
+  uint32_t w[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float a0 = v[2 * j] * rcp, b0 = v[2 * j + 1] * rcp;
+    const float a1 = fmaf(fmaf(-a0, sf, v[2 * j]), rcp, a0), b1 = fmaf(fmaf(-b0, sf, v[2 * j + 1]), rcp, b0);
+    w[j] = __nv_cvt_float2_to_fp8x2(make_float2(a1, b1), __NV_SATFINITE, __NV_E4M3);
+  }
+  uint2 pk;
+  pk.x = (w[0] & 0xFFFFu) | (w[1] << 16);
+  pk.y = (w[2] & 0xFFFFu) | (w[3] << 16);
+  return pk;
+}
 __device__ __forceinline__ __half make_scale(float amax, float upper) {
   __half sh = __float2half_rn(__fdiv_rn(amax, upper));
   if (__half2float(sh) == 0.f) sh = __float2half(1.f);
@@ -105,9 +124,10 @@ __device__ __forceinline__ void quantize_row(Loader ld, int H, int lane, int a_b
     }
     return;
   }
-  const int iupper = (1 << (a_bits - 1)) - 1;
+  const bool e4m3 = a_bits == kBitsE4M3;  // 8-bit float containers (per-token scale only)
+  const int iupper = e4m3 ? 448 : (1 << (a_bits - 1)) - 1;
   const float upper = static_cast<float>(iupper);
-  if (gsize <= 0) {
+  if (gsize <= 0 || e4m3) {
     float amax = 0.f;
     for (int i = lane; i < n8; i += 32) {
       float v[8];
@@ -122,7 +142,7 @@ __device__ __forceinline__ void quantize_row(Loader ld, int H, int lane, int a_b
     for (int i = lane; i < n8; i += 32) {
       float v[8];
       ld(i, v);
-      *reinterpret_cast<uint2*>(o_q8 + i * 8) = quant8(v, sf, rcp, iupper);
+      *reinterpret_cast<uint2*>(o_q8 + i * 8) = e4m3 ? quant8_e4m3(v, sf, rcp) : quant8(v, sf, rcp, iupper);
     }
   } else {  // gsize == 128: 16 lanes x 8 elements per group
     const int iters = (n8 + 31) / 32;

@@ -89,7 +89,7 @@ class MoELayer:
     def _pair_ok(q: QLinearConfig) -> bool:
         if q.w_bits == 16 and q.a_bits == 16:
             return True
-        return q.w_bits == q.a_bits and q.w_bits in (4, 8) and q.w_gsize == -1 and q.w_sym
+        return q.w_bits == q.a_bits and q.w_bits in (4, 8, -8) and q.w_gsize == -1 and q.w_sym  # -8: MXB_BITS_E4M3
 
     def _pack(self, W: torch.Tensor, q: QLinearConfig):
         if q.w_bits == 16:

@@ -23,6 +23,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "lib
 
 EPI_SILU_MUL = 1  # MXB_EPI_SILU_MUL
 PRO_SILU_MUL = 2  # MXB_PRO_SILU_MUL
+BITS_E4M3 = -8    # MXB_BITS_E4M3: a_bits / w_bits code of 8-bit E4M3 containers
 
 
 class MxbError(RuntimeError):
@@ -314,7 +315,7 @@ class Handle:
         scales = torch.empty(ne, dtype=torch.float16, device=W.device)
         self._check(self.lib.mxb_quant_pack_weight(self.h, _ptr(W), N, K, w_bits, a_bits, gsize, int(sym), _ptr(packed),
                                                    _ptr(scales), _stream()), "mxb_quant_pack_weight")
-        return packed.view(N, K * w_bits // 8), scales
+        return packed.view(N, K * abs(w_bits) // 8), scales
 
     def repack_from_ref(self, ref_packed: torch.Tensor, N: int, K: int, w_bits: int, a_bits: int, sym: bool):
         packed = torch.empty(N, K * w_bits // 8, dtype=torch.uint8, device=ref_packed.device)

@@ -107,6 +107,65 @@ def quant_act(X: np.ndarray, bits: int, gsize: int = -1):
     return q, s.reshape(M, K // g)
 
 
+# --------------------------------------------------------------------------- 8-bit float (E4M3) grids
+# The reference only NAMES this kind (`w8a8_g-1_sym_E4M3`, mxmoe/kernels/tile_config.py:45,105,192: MMA_E4M3_K32,
+# USE_FP=True) — it has no quantizer, packer or test for it, so this restatement is "parity unpinned": the definition
+# below is the int path's (quant.py:40-84) with the integer grid replaced by the E4M3 one:
+#   scale = fp16(absmax / 448) (0 -> 1), code = e4m3_rne_satfinite(x / scale), value = code * scale.
+BITS_E4M3 = -8
+E4M3_MAX = 448.0
+
+
+def _e4m3_grid():
+    v = [0.0]
+    for e in range(16):
+        for m in range(8):
+            if e == 15 and m == 7:
+                continue  # NaN
+            v.append((m / 8.0) * 2.0 ** -6 if e == 0 else (1 + m / 8.0) * 2.0 ** (e - 7))
+    g = np.unique(np.array(v, f64))
+    return g
+
+
+_E4M3 = _e4m3_grid()
+
+
+def e4m3_round(x: np.ndarray) -> np.ndarray:
+    """Round to the nearest E4M3 value (ties to the even mantissa), saturating at +-448.  Returns float64 values."""
+    a = np.minimum(np.abs(x.astype(f64)), E4M3_MAX)
+    hi = np.searchsorted(_E4M3, a, side="left").clip(0, len(_E4M3) - 1)
+    lo = (hi - 1).clip(0)
+    dlo, dhi = a - _E4M3[lo], _E4M3[hi] - a
+    # grid index parity == mantissa parity (the grid lists every code in order, 8 mantissas per binade)
+    pick_hi = (dhi < dlo) | ((dhi == dlo) & (hi % 2 == 0))
+    r = np.where(pick_hi, _E4M3[hi], _E4M3[lo])
+    return np.copysign(r, x)
+
+
+def e4m3_encode(v: np.ndarray) -> np.ndarray:
+    """E4M3 values (as produced by e4m3_round) -> byte codes (sign | exponent | mantissa)."""
+    a = np.abs(v.astype(f64))
+    idx = np.searchsorted(_E4M3, a)  # grid index == code of the magnitude (0, subnormals 1..7, then 8 per binade)
+    return (idx.astype(np.uint8) | (np.signbit(v).astype(np.uint8) << 7)).astype(np.uint8)  # -0 keeps its sign, like cvt.rn.satfinite.e4m3x2
+
+
+def quant_e4m3(t: np.ndarray):
+    """Per-row E4M3 quantization of an fp16 [R, K] tensor: returns (values float64 [R,K], scale f16 [R,1])."""
+    assert t.dtype == f16
+    amax = np.abs(t).max(axis=1, keepdims=True)
+    scale = _h_div(amax, np.full_like(amax, E4M3_MAX))
+    scale = np.where(scale == 0, f16(1), scale).astype(f16)
+    return e4m3_round(t.astype(f64) / scale.astype(f64)), scale
+
+
+def gemm_e4m3(vA, sA, vW, sW):
+    """kind::f8f6f4 problem: fp32 accumulation of exact E4M3 products (here float64), then the int path's scale order
+    out = fp16( acc * fp32(fp16(sA * sW)) ) (mm_tile.cuh:472-496)."""
+    acc = (vA @ vW.T).astype(f32)
+    prod = (sA.astype(f16) * sW.astype(f16).reshape(1, -1)).astype(f16)
+    return (acc.astype(f64) * prod.astype(f64)).astype(f32).astype(f16)
+
+
 # --------------------------------------------------------------------------- packed layouts
 def pack_wxax(q: np.ndarray, bits: int) -> np.ndarray:
     """quantize.cuh:424-475: two's-complement values, PACK=16/bits per uint16 along K,
@@ -409,6 +468,10 @@ def run_problem(A: np.ndarray, W: np.ndarray, w_bits, a_bits, gsize, sym):
     if a_bits == 16:
         q, s, z = quant_weight(W, w_bits, gsize, sym)
         return gemm_wonly(A, q, s, z, gsize, sym)
+    if a_bits == BITS_E4M3:
+        va, sa = quant_e4m3(A)
+        vw, sw = quant_e4m3(W)
+        return gemm_e4m3(va, sa, vw, sw)
     qa, sa = quant_act(A, a_bits, gsize)
     qw, sw, _ = quant_weight(W, w_bits, gsize, True)
     return gemm_wxax(qa, sa, qw, sw, gsize)[1]

@@ -66,6 +66,12 @@ def make_problem(ops, rng, M, N, K, w_bits, a_bits, gsize, sym, tile_n=0):
         sc = O.permute_scale(s, None if sym else z, sym)
         p = ops.Problem(dev(A), dev(packed), Cbuf, M, N, K, w_bits, 16, gsize, sym, scale_b=dev(sc), tile_n=tile_n)
         return p, O.gemm_wonly(A, q, s, z, gsize, sym), None
+    if a_bits == O.BITS_E4M3:  # 8-bit float grids (kind::f8f6f4): fp32 accumulation, no integer accumulator to compare
+        va, sa = O.quant_e4m3(A)
+        vw, sw = O.quant_e4m3(W)
+        p = ops.Problem(dev(O.e4m3_encode(va)), dev(O.e4m3_encode(vw)), Cbuf, M, N, K, O.BITS_E4M3, O.BITS_E4M3, -1, True,
+                        scale_a=dev(sa), scale_b=dev(sw.reshape(-1)), tile_n=tile_n)
+        return p, O.gemm_e4m3(va, sa, vw, sw), None
     qa, sa = O.quant_act(A, a_bits, gsize)
     qw, sw, _ = O.quant_weight(W, w_bits, gsize, True)
     acc, out = O.gemm_wxax(qa, sa, qw, sw, gsize)
@@ -431,3 +437,39 @@ def test_select_tiles_reports_the_kernel_choice(H):
     if ch[0].path == 2:
         assert (ch[0].tile_m, ch[0].tile_n) == (256, 192)  # 546 tokens -> 3 equal tiles of 182 -> 192
     assert all(c.est_us > 0 for c in ch)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 128), (300, 512, 2048), (37, 2816, 2048), (546, 2048, 1408)])
+def test_w8a8_e4m3(H, M, N, K):
+    """`w8a8_g-1_sym_E4M3` (tile_config.py:45): E4M3 codes from the oracle, tcgen05.mma kind::f8f6f4 with fp32
+    accumulation, the int path's scale order; both kernels (fixture: auto = CTA pairs, single = one CTA).  The products
+    are exact and only the accumulation order differs from the float64 oracle: max relative error <= 1e-3."""
+    from mxmoe_b200 import ops
+    rng = np.random.default_rng(M + N + K)
+    p, ref, _ = make_problem(ops, rng, M, N, K, O.BITS_E4M3, O.BITS_E4M3, -1, True)
+    H.group_gemm([p])
+    check([p], [ref], [None])
+
+
+def test_e4m3_mixed_list_and_device_quantizers(H):
+    """One launch mixing E4M3, int8 and fp16 problems; the E4M3 operands come from the DEVICE quantizers
+    (mxb_quant_act with a_bits = MXB_BITS_E4M3, mxb_quant_pack_weight): codes and scales bit-exact against the oracle."""
+    from mxmoe_b200 import ops
+    rng = np.random.default_rng(99)
+    M, N, K = 200, 512, 1024
+    A, W = rand16(rng, M, K), rand16(rng, N, K)
+    q8, _, sc = H.quant_act(dev(A), None, M, None, [(ops.BITS_E4M3, -1)])
+    wp, ws = H.quant_pack_weight(dev(W), ops.BITS_E4M3, ops.BITS_E4M3, -1, True)
+    torch.cuda.synchronize()
+    va, sa = O.quant_e4m3(A)
+    vw, sw = O.quant_e4m3(W)
+    assert np.array_equal(q8.cpu().numpy().view(np.uint8), O.e4m3_encode(va))
+    assert np.array_equal(sc.cpu().numpy().view(np.uint16).reshape(-1), sa.view(np.uint16).reshape(-1))
+    assert np.array_equal(wp.cpu().numpy(), O.e4m3_encode(vw))
+    assert np.array_equal(ws.cpu().numpy().view(np.uint16), sw.view(np.uint16).reshape(-1))
+    Cbuf = torch.full((M, N), float("nan"), dtype=torch.float16, device="cuda")
+    p8 = ops.Problem(q8, wp, Cbuf, M, N, K, ops.BITS_E4M3, ops.BITS_E4M3, -1, True, scale_a=sc, scale_b=ws)
+    pi, refi, _ = make_problem(ops, rng, 100, 256, 512, 8, 8, -1, True)
+    pf, reff, _ = make_problem(ops, rng, 64, 128, 256, 16, 16, -1, True)
+    H.group_gemm([p8, pi, pf])
+    check([p8, pi, pf], [O.gemm_e4m3(va, sa, vw, sw), refi, reff], [None, None, None])

@@ -137,3 +137,26 @@ def test_packers_against_live_reference_binary(bits, sym):
         pack = 16 // bits
         assert np.array_equal(O.pack_wxax(a, bits).reshape(-1), o[:16 * K // pack])
         assert np.array_equal(O.pack_wxax(q, bits).reshape(-1), o[16 * K // pack:])
+
+
+def test_e4m3_grid_matches_torch_float8():
+    """The oracle's E4M3 rounding (round to nearest even, saturating) and byte encoding against torch's own
+    float8_e4m3fn conversion on CPU — the only independent implementation in this image; the reference itself only names
+    the kind (tile_config.py:45) and has no quantizer for it."""
+    import torch
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.standard_normal(200000) * 100, rng.standard_normal(50000) * 0.01, [0.0, 448.0, -448.0, 500.0, 2 ** -9, 2 ** -10]])
+    x = x.astype(np.float32)
+    t = torch.from_numpy(x).clamp(-448, 448).to(torch.float8_e4m3fn)
+    r = O.e4m3_round(x)
+    assert np.array_equal(r, t.float().numpy().astype(np.float64))
+    assert np.array_equal(O.e4m3_encode(r), t.view(torch.uint8).numpy())  # including the sign of values that round to zero
+
+
+def test_e4m3_qstr_roundtrip():
+    from mxmoe_b200.config import BITS_E4M3, QLinearConfig
+    q = QLinearConfig.from_qstr("w8a8_g-1_sym_E4M3")
+    assert (q.w_bits, q.a_bits, q.w_gsize, q.w_sym) == (BITS_E4M3, BITS_E4M3, -1, True)
+    assert q.qstr() == "w8a8_g-1_sym_E4M3"
+    with pytest.raises(ValueError):
+        QLinearConfig.from_qstr("w4a4_g-1_sym_E4M3")
