@@ -193,9 +193,15 @@ def main():
     ql = qlayer_for(wl["model"], wl["layer"], wl["q"])
     h = ops.Handle(local)
     if world > 1:
-        from mxmoe_b200.ep import EPMoELayer
+        from mxmoe_b200.ep import EPMoELayer, balanced_expert_order
+        from mxmoe_b200 import workload as Wl
+        # expert placement from the same popularity profile the routing is drawn from (the reference's gate-trace access_freq)
+        kind = "fixture" if wl["model"] == "qwen2_moe" else "uniform"
+        freq = Wl.synthetic_gate_trace(wl["model"], [0], kind)["layer-0"]["access_freq"]
+        order = balanced_expert_order(freq, world) if os.environ.get("MXB_EP_PLACEMENT", "contiguous") == "balanced" else None
+        cfg["placement"] = "popularity-balanced (LPT over the gate trace's access_freq)" if order is not None else "contiguous"
         layer = EPMoELayer(h, s["E"], s["topk"], s["H"], s["I"], s["ns"], ql, max_tokens=T, hadamard_down=wl["hadamard"],
-                           weight_scale=0.05)
+                           weight_scale=0.05, expert_order=order)
     else:
         layer = MoELayer(h, s["E"], s["topk"], s["H"], s["I"], s["ns"], ql, max_tokens=T, hadamard_down=wl["hadamard"],
                          weight_scale=0.05)

@@ -51,6 +51,23 @@ def expert_bounds(E: int, W: int) -> List[int]:
     return [r * E // W for r in range(W + 1)]
 
 
+def balanced_expert_order(freq: Sequence[float], W: int) -> List[int]:
+    """Expert placement from an access-frequency profile (the `access_freq` of the reference's gate trace,
+    moe_tracer.py:189-206): longest-processing-time assignment into the W contiguous slices of expert_bounds — most
+    popular expert first, each to the least loaded rank that still has a free slot.  Returns the expert order; rank r owns
+    order[bounds[r]:bounds[r+1]].  With contiguous placement the step waits for the rank that holds the popular experts."""
+    E = len(freq)
+    bounds = expert_bounds(E, W)
+    cap = [bounds[r + 1] - bounds[r] for r in range(W)]
+    load = [0.0] * W
+    slots: List[List[int]] = [[] for _ in range(W)]
+    for e in sorted(range(E), key=lambda i: (-float(freq[i]), i)):
+        r = min((r for r in range(W) if len(slots[r]) < cap[r]), key=lambda r: (load[r], r))
+        slots[r].append(e)
+        load[r] += float(freq[e])
+    return [e for r in range(W) for e in sorted(slots[r])]
+
+
 def ep_plan(counts: np.ndarray, bounds: Sequence[int], rank: int):
     """Split sizes of the dispatch from the all-gathered count matrix counts[src_rank, expert].
 
@@ -68,12 +85,18 @@ class EPMoELayer(MoELayer):
     def __init__(self, handle: ops.Handle, E: int, topk: int, H: int, I: int, ns: int, qlayer: QLayerConfig, max_tokens: int,
                  hadamard_down: bool = False, capacity: float = 2.0, seed: int = 42, weight_scale: float = 1.0,
                  group: Optional[dist.ProcessGroup] = None, weights: Optional[dict] = None, overlap_shared: bool = True,
-                 comm_sms: int = 20, exchange: str = "auto"):
+                 comm_sms: int = 20, exchange: str = "auto", expert_order: Optional[Sequence[int]] = None):
+        """expert_order: placement of the experts (default 0..E-1): rank r owns expert_order[bounds[r]:bounds[r+1]]
+        (balanced_expert_order builds one from a popularity profile).  Internally experts are relabelled by their position
+        in the order, so every kernel still sees contiguous slices; topk_ids keep the caller's numbering."""
         self.group = group
         self.W = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.bounds = expert_bounds(E, self.W)
-        mine = list(range(self.bounds[self.rank], self.bounds[self.rank + 1]))
+        order = list(expert_order) if expert_order is not None else list(range(E))
+        assert sorted(order) == list(range(E)), "expert_order must be a permutation of the experts"
+        self.order = order
+        mine = order[self.bounds[self.rank]:self.bounds[self.rank + 1]]
         self.T_local = max_tokens
         if exchange == "auto":
             exchange = "push" if (self.W > 1 and dist.get_backend(group) == "nccl") else "nccl"
@@ -82,7 +105,7 @@ class EPMoELayer(MoELayer):
         # receive capacity in rows: `capacity` x the balanced share (NCCL path, checked on the host every step);
         # the push path cannot check before it writes into a peer, so it holds the worst case
         self.cap_rows = max_tokens * topk * self.W if self.push else int(max_tokens * topk * capacity) + 128
-        self.q_all = [(qlayer.experts[str(e)].gate.a_bits, qlayer.experts[str(e)].gate.a_gsize) for e in range(E)]
+        self.q_all = [(qlayer.experts[str(e)].gate.a_bits, qlayer.experts[str(e)].gate.a_gsize) for e in order]  # by position
         self.sender_quant = all(a < 16 for a, _ in self.q_all)
         self.any_g128 = any(g == 128 for a, g in self.q_all if a < 16)
         cap_tokens = (self.cap_rows + topk - 1) // topk
@@ -91,6 +114,9 @@ class EPMoELayer(MoELayer):
         super().__init__(handle, E, topk, H, I, ns, qlayer, max_tokens=cap_tokens, hadamard_down=hadamard_down,
                          expert_ids=mine, seed=seed + 1000 * self.rank, weight_scale=weight_scale, weights=weights)
         d = self.dev
+        relabel = np.empty(E, dtype=np.int32)
+        relabel[np.asarray(order)] = np.arange(E, dtype=np.int32)
+        self.relabel = None if order == list(range(E)) else torch.from_numpy(relabel).to(d)
         R = max_tokens * topk
         cols = H // 128 if self.any_g128 else 1
         if self.sender_quant and self.x_sc.shape[1] != cols:  # receive buffer must match the senders' scale width
@@ -244,6 +270,8 @@ class EPMoELayer(MoELayer):
         dist.all_to_all_single(out, inp, output_split_sizes=out_splits, input_split_sizes=in_splits, group=self.group)
 
     def forward(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: Optional[torch.Tensor] = None):
+        if self.relabel is not None:  # caller's expert ids -> positions in the placement order
+            topk_ids = self.relabel[topk_ids.long()]
         if self.push:
             return self._forward_push(x, topk_ids, topk_w, out)
         return self._forward_nccl(x, topk_ids, topk_w, out)

@@ -88,3 +88,21 @@ def test_ep_plan_shapes():
     counts = np.arange(8 * 60).reshape(8, 60)
     send, recv, seg = ep_plan(counts, b, 3)
     assert sum(send) == counts[3].sum() and sum(recv) == counts[:, b[3]:b[4]].sum() and len(seg) == 8 * (b[4] - b[3])
+
+
+def test_balanced_expert_order_is_a_permutation_and_balances():
+    """Placement from a popularity profile: every rank keeps its slice SIZE (expert_bounds), the most loaded rank gets
+    closer to the mean than with contiguous placement, and the result is a permutation (the relabelling is exact)."""
+    import numpy as np
+    from mxmoe_b200 import workload as Wl
+    from mxmoe_b200.ep import balanced_expert_order, expert_bounds
+    freq = np.array(Wl.synthetic_gate_trace("qwen2_moe", [0], "fixture")["layer-0"]["access_freq"], dtype=np.float64)
+    E = len(freq)
+    for W in (2, 4, 8):
+        order = balanced_expert_order(freq, W)
+        assert sorted(order) == list(range(E))
+        b = expert_bounds(E, W)
+        cont = max(freq[b[r]:b[r + 1]].sum() for r in range(W))
+        bal = max(freq[order[b[r]:b[r + 1]]].sum() for r in range(W))
+        assert bal <= cont + 1e-12
+    assert balanced_expert_order([1.0] * 6, 3) == [0, 3, 1, 4, 2, 5]

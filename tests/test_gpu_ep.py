@@ -47,7 +47,8 @@ def _worker(rank, world, port, mixed_f16, exchange, E, q):
             Ie = I * ns if e == E else I
             weights[e] = (((torch.rand(2 * Ie, Hd, generator=g) * 2 - 1) * 0.12).half(), ((torch.rand(Hd, Ie, generator=g) * 2 - 1) * 0.18).half())
         h = ops.Handle(rank)
-        ep = EPMoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, hadamard_down=False, weights=weights, exchange=exchange)
+        ep = EPMoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, hadamard_down=False, weights=weights, exchange=exchange,
+                        expert_order=[(3 * i + 1) % E for i in range(E)] if E == 7 else None)  # E = 7: a scattered placement
         full = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=weights)
         rng = np.random.default_rng(10 + rank)
         x = torch.from_numpy((rng.random((T, Hd)) * 2 - 1).astype(np.float16)).cuda()
