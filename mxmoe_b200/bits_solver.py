@@ -122,6 +122,29 @@ def strategy_bits(qstr: str) -> Tuple[int, int]:
     return abs(q.w_bits), abs(q.a_bits)
 
 
+def cost_from_table(table: dict, layer_workload: Dict[str, list], strategies: Sequence[str]) -> Optional[np.ndarray]:
+    """cost[e][n][s] from a MEASURED table (tools/cost_table.py -> profiles/cost_table_b200_r01.json: per strategy and block,
+    microseconds of one expert problem at a ladder of row counts), log-log interpolated in the row count.  The table plays
+    the part of the reference's perf/performance_table.json (bits_solver.py:533-541).  None if a strategy is missing."""
+    gu, dn = layer_workload["gate_up"], layer_workload["down"]
+    E = len(gu)
+    cost = np.zeros((E, 3, len(strategies)))
+    for s, qs in enumerate(strategies):
+        ent = table.get("strategies", {}).get(qs)
+        if ent is None:
+            return None
+        for blk, lst, cols in (("gate_up", gu, (0, 1)), ("down", dn, (2,))):
+            pts = sorted((int(k.split(":")[1]), v["measured_us"], v["shape"]) for k, v in ent.items() if k.startswith(blk + ":"))
+            ms, us = np.log([p[0] for p in pts]), np.log([p[1] for p in pts])
+            n_ref = pts[0][2][1]
+            for e, p in enumerate(lst):
+                M, N, _ = p["shape"]
+                t = float(np.exp(np.interp(np.log(max(M, 1)), ms, us))) * (N / n_ref)  # wider experts (shared): linear in N
+                for c in cols:
+                    cost[e, c, s] = t / len(cols)
+    return cost
+
+
 def runtime_cost(model: str, layer_workload: Dict[str, list], strategies: Sequence[str], handle=None) -> np.ndarray:
     """cost[e][n][s] in microseconds from the library's own selector (mxb_select_tiles: kernel path, tile and roofline
     time per problem).  gate and up are one fused GEMM (N = 2I): its estimate is split evenly between the two blocks,
@@ -168,7 +191,8 @@ def synthetic_loss(E: int, strategies: Sequence[str], access_prob: Sequence[floa
 
 
 def solve_model(model: str, strategies: Sequence[str], wbits: float, batch: int, r: float = 1.0, layers: Optional[Sequence[int]] = None,
-                loss: Optional[Dict[str, np.ndarray]] = None, trace_kind: str = "fixture", seed: int = 0):
+                loss: Optional[Dict[str, np.ndarray]] = None, trace_kind: str = "fixture", seed: int = 0,
+                cost_table: Optional[dict] = None):
     """Layer-by-layer allocation (solve_model_qconfig_layer_level).  Returns (qconfig dict in the reference schema, LT)."""
     s = C.MODEL_SHAPES[model]
     layers = list(layers) if layers is not None else [0]
@@ -183,7 +207,12 @@ def solve_model(model: str, strategies: Sequence[str], wbits: float, batch: int,
         key = f"layer-{li}"
         freq = list(trace[key]["access_freq"]) + ([float(np.mean(trace[key]["access_freq"])) * s["topk"]] if s["ns"] else [])
         d = loss[str(li)] if loss is not None else synthetic_loss(units, strategies, freq, seed + li)
-        cost = runtime_cost(model, W.generate_workload_from_gate_trace(trace, batch, li)[key], strategies) if r < 1.0 else None
+        cost = None
+        if r < 1.0:
+            lw = W.generate_workload_from_gate_trace(trace, batch, li)[key]
+            cost = cost_from_table(cost_table, lw, strategies) if cost_table is not None else None
+            if cost is None:  # no measured table (or a strategy it lacks): the selector's roofline estimate
+                cost = runtime_cost(model, lw, strategies)
         assign, L, T = solve_layer(d, mem, budget, cost, r)
         experts = {}
         for e in range(units):
@@ -216,12 +245,14 @@ def main(argv=None):
     ap.add_argument("--layers", type=int, nargs="*", default=[11])
     ap.add_argument("--filter_list", nargs="+", default=["w4a4_g-1_sym", "w8a8_g-1_sym"])
     ap.add_argument("--loss", default=None, help="JSON {layer: [E][3][S]} of calibration losses; default synthetic")
+    ap.add_argument("--cost_table", default=None, help="measured table from tools/cost_table.py; default: mxb_select_tiles estimates")
     ap.add_argument("--out", default=None)
     a = ap.parse_args(argv)
     loss = None
     if a.loss:
         loss = {k: np.asarray(v) for k, v in json.load(open(a.loss)).items()}
-    q = solve_model(a.model, a.filter_list, a.wbits, a.batch, a.r, a.layers, loss)
+    table = json.load(open(a.cost_table)) if a.cost_table else None
+    q = solve_model(a.model, a.filter_list, a.wbits, a.batch, a.r, a.layers, loss, cost_table=table)
     print(f"average weight bits {average_wbits(q, a.model):.3f} (target {a.wbits}); LT {q['LT']}")
     if a.out:
         json.dump(q, open(a.out, "w"))

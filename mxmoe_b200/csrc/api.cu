@@ -884,17 +884,25 @@ extern "C" int mxb_select_tiles(mxb_handle_t c, const MxbProblem* problems, int 
       const double tiles = double((p.M + 127) / 128) * double((p.N + t.tile_n - 1) / t.tile_n);
       const double kb = double((p.K + k.k_per_block - 1) / k.k_per_block);
       double cyc = tiles * kb * 4.0 * (128.0 * t.tile_n / 256.0);
-      if (k.epi == mxb::EPI_INT_GROUP) cyc *= 2.0;  // epilogue-paced: one TMEM drain per 128-K group
       t_tensor = cyc / (sms * clk);
+      // Kinds paced by something other than the tensor pipe, at the rates measured on this pool
+      // (profiles/cost_table_b200_r01.json, M = 8192): group-wise int scales drain TMEM once per 128-K group (274 TOPS);
+      // weight-only kinds wait for the converter warps (4-bit 420 TOPS, 8-bit alike)
+      const double ops = 2.0 * double((p.M + 127) / 128 * 128) * p.N * p.K;
+      if (k.epi == mxb::EPI_INT_GROUP) t_tensor = ops / 274e12;
+      else if (k.conv >= mxb::CONV_W4_F16) t_tensor = ops / 420e12;
       t_l2 = tiles * kb * (128.0 * 128.0 + t.tile_n * double(k.b_bytes_per_kb)) / l2;
       if (stream) t_tensor = t_l2 = 0.0;
     }
     const double bytes = w_bytes + double(p.M) * p.K * a_el + double(p.M) * p.N * 2.0;
     double t_mem = bytes / hbm;
-    if (stream) t_mem = w_bytes / 1.7e12;  // the streaming kernel is instruction-bound at ~1.7 TB/s (profiles/)
+    // the streaming kernel is instruction-bound at ~2.6 TB/s per 16-token pass (profiles/ncu_w4a16_stream_r01.txt)
+    if (stream) t_mem = w_bytes * double((p.M + 15) / 16) / 2.6e12;
     double tt = t_tensor > t_mem ? t_tensor : t_mem;
     if (t_l2 > tt) tt = t_l2;
-    t.est_us = float(1e6 * tt);
+    // fixed cost of a problem inside a launch (tile-table entry, pipeline fill and drain of its first tile): ~1.3 us
+    // measured on 8-expert lists of tiny problems
+    t.est_us = float(1e6 * tt + 1.3);
     out[i] = t;
   }
   return MXB_OK;

@@ -86,3 +86,27 @@ def test_tradeoff_moves_along_the_pareto_front():
     q1 = solve_model("qwen2_moe", ["w4a4_g-1_sym", "w8a8_g-1_sym"], 5.0, 8192, r=0.5, layers=[11])
     q0 = solve_model("qwen2_moe", ["w4a4_g-1_sym", "w8a8_g-1_sym"], 5.0, 8192, r=0.0, layers=[11])
     assert q0["LT"]["11"][1] <= q1["LT"]["11"][1] + 1e-9
+
+
+def test_measured_cost_table_drives_the_solver():
+    """profiles/cost_table_b200_r01.json (tools/cost_table.py on B200: measured microseconds per expert problem and
+    strategy) as the runtime model, the role of the reference's perf/performance_table.json: log-log interpolation in the
+    row count is monotone, and the runtime-only optimum (r = 0) prefers the measured-faster strategy wherever the budget
+    allows."""
+    from mxmoe_b200 import workload as Wl
+    from mxmoe_b200.bits_solver import cost_from_table, solve_model
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    table = json.load(open(os.path.join(root, "profiles", "cost_table_b200_r01.json")))
+    trace = Wl.synthetic_gate_trace("qwen2_moe", [11], "fixture")
+    lw = Wl.generate_workload_from_gate_trace(trace, 8192, 11)["layer-11"]
+    strategies = ["w4a4_g-1_sym", "w8a8_g-1_sym"]
+    cost = cost_from_table(table, lw, strategies)
+    assert cost.shape == (61, 3, 2) and (cost > 0).all()
+    rows = np.array([p["shape"][0] for p in lw["gate_up"][:60]])
+    order = np.argsort(rows)
+    assert np.all(np.diff(cost[:60, 0, 1][order]) >= -1e-9)       # more rows never cost less
+    assert cost_from_table(table, lw, ["w2a16_g128_asym"]) is None  # unknown strategy -> caller falls back to the selector
+    q = solve_model("qwen2_moe", strategies, 8.0, 8192, r=0.0, layers=[11], cost_table=table)
+    picked8 = sum(1 for e in q["11"]["experts"].values() if e["down"]["w_bits"] == 8)
+    faster8 = int((cost[:, 2, 1] < cost[:, 2, 0]).sum())
+    assert picked8 >= faster8  # with a budget of 8 bits nothing stops the faster choice
