@@ -203,6 +203,11 @@ int mxb_quant_act_push(mxb_handle_t h, const void* x, int H, const int32_t* src_
 /* out[t] = fp16( sum_j topk_w[t,j] * down_out[slot_of[t,j]] (+ shared_out[t]) ), fp32 accumulation in j order. */
 int mxb_combine(mxb_handle_t h, const void* down_out, int H, const int32_t* slot_of, const float* topk_w, int T,
                 int k, const void* shared_out, void* out, void* stream);
+/* As mxb_combine with the shared expert's output scaled per token: out[t] = sum_j w[t,j] * down[slot(t,j)] +
+ * shared_scale[t] * shared_out[t] (fp32 accumulation).  shared_scale is sigmoid(shared_expert_gate(x)) of
+ * Qwen2MoeSparseMoeBlock; NULL = 1 (the behaviour of mxb_combine). */
+int mxb_combine_gated(mxb_handle_t h, const void* down_out, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
+                      const void* shared_out, const float* shared_scale, void* out, void* stream);
 
 /* ---- offline weight path ---- */
 /* W fp16 [N,K] -> native packed weights + scales for (w_bits, a_bits, gsize, sym); numerics of

@@ -767,7 +767,18 @@ int mxb_combine(mxb_handle_t c, const void* down_out, int H, const int32_t* slot
   if (T < 0 || k < 1 || H % 8 != 0) return fail(MXB_EINVAL, "bad combine shape T=%d k=%d H=%d", T, k, H);
   if (T > 0 && (!down_out || !slot_of || !topk_w || !out)) return fail(MXB_EINVAL, "null pointer");
   CU_OK(cudaSetDevice(c->device));
-  CU_OK(mxb::combine_launch(down_out, H, slot_of, topk_w, T, k, shared_out, out, static_cast<cudaStream_t>(stream)));
+  CU_OK(mxb::combine_launch(down_out, H, slot_of, topk_w, T, k, shared_out, nullptr, out, static_cast<cudaStream_t>(stream)));
+  return MXB_OK;
+}
+
+int mxb_combine_gated(mxb_handle_t c, const void* down_out, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
+                      const void* shared_out, const float* shared_scale, void* out, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (T < 0 || k < 1 || H % 8 != 0) return fail(MXB_EINVAL, "bad combine shape T=%d k=%d H=%d", T, k, H);
+  if (T > 0 && (!down_out || !slot_of || !topk_w || !out)) return fail(MXB_EINVAL, "null pointer");
+  if (shared_scale && !shared_out) return fail(MXB_EINVAL, "shared_scale without shared_out");
+  CU_OK(cudaSetDevice(c->device));
+  CU_OK(mxb::combine_launch(down_out, H, slot_of, topk_w, T, k, shared_out, shared_scale, out, static_cast<cudaStream_t>(stream)));
   return MXB_OK;
 }
 

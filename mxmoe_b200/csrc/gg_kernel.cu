@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
   if (warp == 0) {
     // ============================================================ TMA producer
     if (lane == 0) {
-      int stage = 0;
+      int stage = 0, desc_p = -1;
       uint32_t phase = 0;
       for (TileWalk w(S.prefix, P); w.valid(); w.advance()) {
         const DevProblem& d = probs[w.p];
@@ -184,6 +184,11 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
         const uint32_t tx = d.tx_bytes;
         const bool has_conv = d.conv != CONV_NONE;
         const int b_off = has_conv ? GG_PACKED_OFF : 0;
+        if (w.p != desc_p) {  // first tile of this problem on this CTA: drop any stale cached descriptor (ptx.cuh)
+          tma_desc_acquire(&d.tmA);
+          tma_desc_acquire(&d.tmB);
+          desc_p = w.p;
+        }
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&S.empty[stage], phase ^ 1);
           uint8_t* sa = S.stages + stage * GG_STAGE_BYTES;
@@ -259,7 +264,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
       const int M = S.m_arr[w.p], N = d.N, bn = d.bn;
       const int row_in_prob = m_blk * GG_BM + q * 32 + lane;
       const int grow = S.row0[w.p] + row_in_prob;           // global row of this lane
-      const int crow = (d.c_row != nullptr ? __ldg(d.c_row) : S.row0[w.p]) + row_in_prob;  // its row in C (DevProblem::c_row)
+      const int crow = (d.c_row != nullptr ? static_cast<int>(ld_nc_u32(d.c_row)) : S.row0[w.p]) + row_in_prob;  // its row in C (DevProblem::c_row)
       const bool row_ok = row_in_prob < M;
       const int rows_valid = M - (m_blk * GG_BM + q * 32);  // rows of this warp inside the problem
       const int n0 = n_blk * bn;
@@ -296,7 +301,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               uint4 s4 = make_uint4(0, 0, 0, 0);
-              if (col0 + g * 8 < N) s4 = __ldg(reinterpret_cast<const uint4*>(sb + col0 + g * 8));
+              if (col0 + g * 8 < N) s4 = ld_nc_v4(sb + col0 + g * 8);
               const uint32_t sw[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
@@ -345,7 +350,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
 #pragma unroll
               for (int gg = 0; gg < 4; ++gg) {
                 uint4 s4 = make_uint4(0, 0, 0, 0);
-                if (col0 + gg * 8 < N) s4 = __ldg(reinterpret_cast<const uint4*>(sbg + col0 + gg * 8));
+                if (col0 + gg * 8 < N) s4 = ld_nc_v4(sbg + col0 + gg * 8);
                 const uint32_t sw[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {

@@ -188,7 +188,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
     // wraps every UTMALDG in a uniform-register "waterfall" loop, and one thread issuing 5 loads per stage was the
     // limiter of the first version of this kernel (ncu: producer busy 64 % of the time, converters starved).
     const bool tokens = warp == 0;
-    int stage = 0;
+    int stage = 0, desc_p = -1;
     uint32_t phase = 0;
     PairTile t;
     for (PairWalk w(S, P); w.next(&t);) {
@@ -206,6 +206,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       // bytes counted on the leader's `full`: the token boxes of both CTAs (+ both weight halves when unconverted)
       const uint32_t tx_full = 2u * tok_bytes + (has_conv ? 0u : 2u * GP_W_BYTES);
       const CUtensorMap* tmT = big ? &d.tmA2 : &d.tmA;
+      if (t.p != desc_p) {  // first tile of this problem on this CTA: drop any stale cached descriptor (ptx.cuh); every lane
+        tma_desc_acquire(&d.tmA);  // fences, elect_one() may pick any of them to issue
+        tma_desc_acquire(&d.tmA2);
+        tma_desc_acquire(&d.tmB);
+        desc_p = t.p;
+        __syncwarp();
+      }
       for (int kb = 0; kb < kblocks; ++kb) {
         mbar_wait(&S.empty[stage], phase ^ 1);
         uint8_t* sw = S.stages + stage * GP_STAGE_BYTES;
@@ -300,7 +307,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       const bool facc = d.mma_kind == MMA_F8;
       const int grow0 = S.row0[t.p] + t.t0;  // global row of the tile's first token
       // C may start at another row than A (DevProblem::c_row): results written straight into a peer GPU's buffer
-      const int crow0 = (d.c_row != nullptr ? __ldg(d.c_row) : S.row0[t.p]) + t.t0;
+      const int crow0 = (d.c_row != nullptr ? static_cast<int>(ld_nc_u32(d.c_row)) : S.row0[t.p]) + t.t0;
       __half* sa_buf = S.sa_stage + acc * GP_BT;
       __half2 sb2 = __float2half2_rn(1.f);
       if (epi == EPI_INT_ROWCOL) {

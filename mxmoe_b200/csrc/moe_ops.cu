@@ -272,7 +272,8 @@ cudaError_t ep_plan_launch(const int32_t* counts, int W, int rank, int E, void* 
 namespace {
 __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__ down, int H, const int32_t* __restrict__ slot_of,
                                                        const float* __restrict__ topk_w, int T, int k,
-                                                       const __half* __restrict__ shared_out, __half* __restrict__ out) {
+                                                       const __half* __restrict__ shared_out,
+                                                       const float* __restrict__ shared_scale, __half* __restrict__ out) {
   // one thread per (token, 8 output elements): a decode step (T of a few dozen) still spreads over the whole chip, and
   // the k gathered rows of a thread are independent loads in flight together
   const int n8 = H >> 3;
@@ -307,8 +308,10 @@ __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__
   if (shared_out != nullptr) {
     uint4 v = *reinterpret_cast<const uint4*>(shared_out + static_cast<int64_t>(t) * H + i * 8);
     const __half* vh = reinterpret_cast<const __half*>(&v);
+    // Qwen's shared-expert gate: sigmoid(shared_expert_gate(x)) per token, applied to the fp16 shared output
+    const float ss = shared_scale != nullptr ? shared_scale[t] : 1.f;
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = acc[e] + __half2float(vh[e]);
+    for (int e = 0; e < 8; ++e) acc[e] = shared_scale != nullptr ? fmaf(ss, __half2float(vh[e]), acc[e]) : acc[e] + __half2float(vh[e]);
   }
   uint4 pk;
   __half2* ph = reinterpret_cast<__half2*>(&pk);
@@ -319,11 +322,11 @@ __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__
 }  // namespace
 
 cudaError_t combine_launch(const void* down, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
-                           const void* shared_out, void* out, cudaStream_t st) {
+                           const void* shared_out, const float* shared_scale, void* out, cudaStream_t st) {
   if (T == 0) return cudaSuccess;
   const int64_t units = static_cast<int64_t>(T) * (H >> 3);
   combine_kernel<<<static_cast<unsigned>((units + 255) / 256), 256, 0, st>>>(static_cast<const __half*>(down), H, slot_of, topk_w, T, k,
-                                                                           static_cast<const __half*>(shared_out), static_cast<__half*>(out));
+                                                                           static_cast<const __half*>(shared_out), shared_scale, static_cast<__half*>(out));
   return cudaGetLastError();
 }
 

@@ -33,7 +33,7 @@ cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t
                                   bool any_g128, cudaStream_t st);
 
 cudaError_t combine_launch(const void* down, int H, const int32_t* slot_of, const float* topk_w, int T, int k,
-                           const void* shared_out, void* out, cudaStream_t st);
+                           const void* shared_out, const float* shared_scale, void* out, cudaStream_t st);
 
 cudaError_t quant_pack_weight_launch(const void* W, int N, int K, int bits, int gsize, int sym, int layout, void* packed,
                                      void* scales, cudaStream_t st);

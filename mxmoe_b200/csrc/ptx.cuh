@@ -73,6 +73,13 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
 }
+// A tensor map that lives in global memory (DevProblem::tmA/tmB, uploaded with cudaMemcpyAsync) is read through the
+// tensormap proxy, which caches descriptors by address.  A plan slot that is re-uploaded, or a new plan allocated at the
+// address of a freed one, would otherwise be served from the stale cached descriptor (old base pointer, old box):
+// the thread that issues the loads acquires the descriptor once per (CTA, problem) before its first use.
+__device__ __forceinline__ void tma_desc_acquire(const void* tmap) {
+  asm volatile("fence.proxy.tensormap::generic.acquire.sys [%0], 128;" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
+}
 // 2-D tiled load, completes `bytes` on the mbarrier.  c0 = innermost (K) coordinate, c1 = row.
 __device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1) {
   asm volatile(
@@ -311,6 +318,24 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
 }
 __device__ __forceinline__ void st_global_v4(void* p, uint4 v) {
   asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// Read-only loads as volatile asm: nvcc hoists __ldg() out of the branch that guards it (it treats ld.global.nc as safe to
+// speculate) and then reads past the end of a short buffer or through a null pointer: an illegal address whenever the
+// buffer happens to be the last block of a mapped segment.  A volatile asm stays under its guard.
+__device__ __forceinline__ uint32_t ld_nc_u16(const void* p) {
+  uint16_t r;
+  asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_nc_u32(const void* p) {
+  uint32_t r;
+  asm volatile("ld.global.nc.u32 %0, [%1];" : "=r"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {  // L1-allocating variant (reused scale vectors)
+  uint4 r;
+  asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
 }
 __device__ __forceinline__ uint4 ld_global_nc_v4(const void* p) {
   uint4 r;

@@ -106,6 +106,7 @@ __device__ __forceinline__ int ws_first_slab(const WsEntry& e, int warp) { retur
 struct WsProd {
   int i, slab, ks;
   bool live;
+  int desc_p;  // problem whose weight descriptor this lane acquired last (tma_desc_acquire, ptx.cuh)
 };
 
 // first entry at or after c.i this warp has a slab in
@@ -176,11 +177,11 @@ __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& 
     if (kl >= K) return;
     const int64_t gi = static_cast<int64_t>(pb.gsz == K ? 0 : kl >> 7) * N + slab * WS_SLAB + g;
     if (pb.sym) {
-      nraw0 = __half_as_ushort(__ldg(pb.sb + gi));
-      nraw1 = __half_as_ushort(__ldg(pb.sb + gi + 8));
+      nraw0 = ld_nc_u16(pb.sb + gi);  // (not __ldg: nvcc speculates it past the bounds this lambda is called under)
+      nraw1 = ld_nc_u16(pb.sb + gi + 8);
     } else {
-      nraw0 = __ldg(reinterpret_cast<const uint32_t*>(pb.sb) + gi);
-      nraw1 = __ldg(reinterpret_cast<const uint32_t*>(pb.sb) + gi + 8);
+      nraw0 = ld_nc_u32(reinterpret_cast<const uint32_t*>(pb.sb) + gi);
+      nraw1 = ld_nc_u32(reinterpret_cast<const uint32_t*>(pb.sb) + gi + 8);
     }
   };
   const int slab0 = ws_first_slab(e, warp);
@@ -224,6 +225,10 @@ __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& 
       __syncwarp();  // every lane is done reading the slot
       if (lane == 0 && prod.live) {  // refill the slot just freed (the producer's next slot IS this one: ring order)
         const WsEntry pe = ent[prod.i];
+        if (pe.p != prod.desc_p) {
+          tma_desc_acquire(&probs[pe.p].tmB);
+          prod.desc_p = pe.p;
+        }
         mbar_expect_tx(&full[pslot], WS_STAGE_BYTES);
         tma_load_2d(const_cast<uint8_t*>(ring) + pslot * WS_STAGE_BYTES, &probs[pe.p].tmB, &full[pslot], prod.ks * (WS_STAGE_K / 2),
                     prod.slab * WS_SLAB);
@@ -412,11 +417,15 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
     p_next = ctl[1];
 
     // producer: request the first `stages` boxes of this list
-    WsProd prod = {0, 0, 0, false};
+    WsProd prod = {0, 0, 0, false, -1};
     if (lane == 0) {
       ws_prod_seek(prod, ent, n_ent, warp);
       for (int s = 0; s < stages && prod.live; ++s) {
         const WsEntry pe = ent[prod.i];
+        if (pe.p != prod.desc_p) {
+          tma_desc_acquire(&probs[pe.p].tmB);
+          prod.desc_p = pe.p;
+        }
         mbar_expect_tx(&full[pslot], WS_STAGE_BYTES);
         tma_load_2d(ring + pslot * WS_STAGE_BYTES, &probs[pe.p].tmB, &full[pslot], prod.ks * (WS_STAGE_K / 2), prod.slab * WS_SLAB);
         if (++pslot == static_cast<uint32_t>(stages)) pslot = 0;

@@ -201,14 +201,16 @@ class MoELayer:
     def actq_dn(self):
         return [(e.q_dn.a_bits, e.q_dn.a_gsize) for e in self.experts[:self.EL]]
 
-    def forward(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: Optional[torch.Tensor] = None):
-        """x fp16 [T,H]; topk_ids int32 [T,k] in [0,E) (all experts local); topk_w fp32 [T,k] -> fp16 [T,H]."""
+    def forward(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: Optional[torch.Tensor] = None,
+                shared_scale: Optional[torch.Tensor] = None):
+        """x fp16 [T,H]; topk_ids int32 [T,k] in [0,E) (all experts local); topk_w fp32 [T,k] -> fp16 [T,H].
+        shared_scale: optional fp32 [T] gate of the shared expert (Qwen: sigmoid(shared_expert_gate(x)))."""
         T = x.shape[0]
         assert T <= self.max_tokens and self.EL == self.E, "use forward_rows for an expert-parallel shard"
         h = self.h
         _, src, slot = h.permute(topk_ids, self.E, self.offs, self.src[:T * self.topk], self.slot[:T])
         self.run_experts(x, src, T * self.topk, T)
-        return h.combine(self.dn_out, slot, topk_w, self.s_dn if self.ns else None, out)
+        return h.combine(self.dn_out, slot, topk_w, self.s_dn if self.ns else None, out, shared_scale if self.ns else None)
 
     def capture(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: torch.Tensor):
         """CUDA-graph one step over FIXED buffers and return the graph (`g.replay()` re-runs it on new contents).

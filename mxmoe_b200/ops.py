@@ -75,6 +75,7 @@ EXPORTS = [
     ("mxb_ep_plan", _I, [_P, _P, _I, _I, _I, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), _P, _P, _P, _P]),
     ("mxb_quant_act_push", _I, [_P, _P, _I, _P, _I, _P, C.POINTER(MxbActQ), _I, _P, _I, _I, _P]),
     ("mxb_combine", _I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _P]),
+    ("mxb_combine_gated", _I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _P, _P]),
     ("mxb_quant_pack_weight", _I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     ("mxb_repack_from_ref", _I, [_P, _P, _I, _I, _I, _I, _I, _P, _P]),
     ("mxb_interleave_gate_up", _I, [_P, _P, _I, _I64, _P, _P]),
@@ -296,11 +297,16 @@ class Handle:
                                                 _ptr(out_f16), _ptr(scales), cols, _stream()), "mxb_silu_mul_quant")
         return out_q8, out_f16, scales
 
-    def combine(self, down_out, slot_of, topk_w, shared_out=None, out=None):
+    def combine(self, down_out, slot_of, topk_w, shared_out=None, out=None, shared_scale=None):
+        """shared_scale: optional fp32 [T] multiplying the shared expert's rows (Qwen's sigmoid shared-expert gate)"""
         T, k = slot_of.shape
         H = down_out.shape[-1]
         if out is None:
             out = torch.empty(T, H, dtype=torch.float16, device=down_out.device)
+        if shared_scale is not None:
+            self._check(self.lib.mxb_combine_gated(self.h, _ptr(down_out), H, _ptr(slot_of), _ptr(topk_w), T, k, _ptr(shared_out),
+                                                   _ptr(shared_scale), _ptr(out), _stream()), "mxb_combine_gated")
+            return out
         self._check(self.lib.mxb_combine(self.h, _ptr(down_out), H, _ptr(slot_of), _ptr(topk_w), T, k, _ptr(shared_out),
                                          _ptr(out), _stream()), "mxb_combine")
         return out
