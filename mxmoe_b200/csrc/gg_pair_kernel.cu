@@ -206,12 +206,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       // bytes counted on the leader's `full`: the token boxes of both CTAs (+ both weight halves when unconverted)
       const uint32_t tx_full = 2u * tok_bytes + (has_conv ? 0u : 2u * GP_W_BYTES);
       const CUtensorMap* tmT = big ? &d.tmA2 : &d.tmA;
-      if (t.p != desc_p) {  // first tile of this problem on this CTA: drop any stale cached descriptor (ptx.cuh); every lane
-        tma_desc_acquire(&d.tmA);  // fences, elect_one() may pick any of them to issue
-        tma_desc_acquire(&d.tmA2);
-        tma_desc_acquire(&d.tmB);
+      if (t.p != desc_p) {  // first tile of this problem on this CTA: drop any stale cached descriptor (ptx.cuh)
+        if (lane < 3) tma_desc_acquire(lane == 0 ? &d.tmA : lane == 1 ? &d.tmA2 : &d.tmB);
         desc_p = t.p;
-        __syncwarp();
+        __syncwarp();  // elect_one() may pick any lane to issue: ordered after the three fences
       }
       for (int kb = 0; kb < kblocks; ++kb) {
         mbar_wait(&S.empty[stage], phase ^ 1);

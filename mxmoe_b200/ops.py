@@ -18,7 +18,8 @@ from typing import List, Optional, Sequence, Tuple
 
 import torch
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmxmoe_b200.so")
+# MXB_LIB: load another build of the same library (A/B runs of a kernel variant); never a different implementation
+_LIB_PATH = os.environ.get("MXB_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libmxmoe_b200.so")
 
 
 EPI_SILU_MUL = 1  # MXB_EPI_SILU_MUL
