@@ -20,6 +20,7 @@
 //
 // Numerics follow the reference epilogue: int32 accumulator -> float, multiplied by the fp16-rounded
 // product sa*sb (mm_tile.cuh:490), accumulated in fp32 per K-group, one rounding to fp16 (mm_tile.cuh:643).
+#include <type_traits>
 #include "gg_kernel.cuh"
 #include "ptx.cuh"
 
@@ -226,26 +227,32 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * 256;
           const int kend = min(kb0 + kpg, kblocks);
-          for (int kb = kb0; kb < kend; ++kb) {
-            mbar_wait(&S.full[stage], phase);
-            if (has_conv) {
-              mbar_wait(&S.conv[stage], (conv_phase_bits >> stage) & 1);
-              conv_phase_bits ^= 1u << stage;
-            }
-            tc_fence_after();
-            const uint32_t a_addr = smem_u32(S.stages + stage * GG_STAGE_BYTES);
-            const uint64_t da = umma_desc_sw128(a_addr);
-            const uint64_t db = umma_desc_sw128(a_addr + GG_A_BYTES);
+          // one copy of the k-block loop per MMA kind (the kind is an opcode): no kind test per MMA on the issuing thread
+          auto run_group = [&](auto kind) {
+            for (int kb = kb0; kb < kend; ++kb) {
+              mbar_wait(&S.full[stage], phase);
+              if (has_conv) {
+                mbar_wait(&S.conv[stage], (conv_phase_bits >> stage) & 1);
+                conv_phase_bits ^= 1u << stage;
+              }
+              tc_fence_after();
+              const uint32_t a_addr = smem_u32(S.stages + stage * GG_STAGE_BYTES);
+              const uint64_t da = umma_desc_sw128(a_addr);
+              const uint64_t db = umma_desc_sw128(a_addr + GG_A_BYTES);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint32_t accum = (kb > kb0 || k > 0) ? 1u : 0u;
-              if (is_i8) umma_i8(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
-              else if (is_f8) umma_f8(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
-              else       umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t accum = (kb > kb0 || k > 0) ? 1u : 0u;
+                if constexpr (decltype(kind)::value == MMA_I8) umma_i8(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+                else if constexpr (decltype(kind)::value == MMA_F8) umma_f8(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+                else umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+              }
+              umma_commit(&S.empty[stage]);
+              if (++stage == GG_STAGES) { stage = 0; phase ^= 1; }
             }
-            umma_commit(&S.empty[stage]);
-            if (++stage == GG_STAGES) { stage = 0; phase ^= 1; }
-          }
+          };
+          if (is_i8) run_group(std::integral_constant<int, MMA_I8>{});
+          else if (is_f8) run_group(std::integral_constant<int, MMA_F8>{});
+          else run_group(std::integral_constant<int, MMA_F16>{});
           umma_commit(&S.tmem_full[acc]);
           if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
@@ -298,6 +305,10 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
                 if (col0 + j < N) ao[j] = static_cast<int32_t>(v[j]) >> shift;
             }
             const __half2 sa2 = __half2half2(sa);
+            if (!facc) {  // integer accumulators become floats in place (one branch per tile, not a select per element)
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__int2float_rn(static_cast<int32_t>(v[j]) >> shift));
+            }
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               uint4 s4 = make_uint4(0, 0, 0, 0);
@@ -307,9 +318,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
               for (int j = 0; j < 4; ++j) {
                 __half2 prod = __hmul2(sa2, *reinterpret_cast<const __half2*>(&sw[j]));
                 float2 pf = __half22float2(prod);
-                const float a0 = facc ? __uint_as_float(v[g * 8 + 2 * j]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j]) >> shift);
-                const float a1 = facc ? __uint_as_float(v[g * 8 + 2 * j + 1]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j + 1]) >> shift);
-                h[g * 4 + j] = pack_half2(a0 * pf.x, a1 * pf.y);
+                h[g * 4 + j] = pack_half2(__uint_as_float(v[g * 8 + 2 * j]) * pf.x, __uint_as_float(v[g * 8 + 2 * j + 1]) * pf.y);
               }
             }
           }

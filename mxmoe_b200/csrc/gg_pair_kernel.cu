@@ -26,6 +26,7 @@
 //
 // Supported here: fp16, w8a8 and w4a4 with per-token / per-channel scales (g-1).  Lists containing
 // group-wise or weight-only problems run on gg_kernel.cu.
+#include <type_traits>
 #include "gg_kernel.cuh"
 #include "ptx.cuh"
 #include "quant_common.cuh"
@@ -254,30 +255,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
         mbar_wait(&S.tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
-        for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&S.full[stage], phase);
-          if (has_conv) {
-            mbar_wait(&S.conv[stage], (conv_phase_bits >> stage) & 1);
-            conv_phase_bits ^= 1u << stage;
-          }
-          tc_fence_after();
-          const uint32_t w_addr = smem_u32(S.stages + stage * GP_STAGE_BYTES);
-          const uint64_t da = umma_desc_sw128(w_addr);
-          const uint64_t db = umma_desc_sw128(w_addr + GP_W_BYTES);
-          if (elect_one()) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-              if (is_i8) umma_i8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
-              else if (is_f8) umma_f8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
-              else       umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+        // The MMA kind is an opcode, not an operand: one copy of the k-block loop per kind, chosen once per tile.  (A kind
+        // test per MMA inside the loop costs 4 % of the whole GEMM: this one lane's issue rate is the kernel's pace.)
+        auto run_tile = [&](auto kind) {
+          for (int kb = 0; kb < kblocks; ++kb) {
+            mbar_wait(&S.full[stage], phase);
+            if (has_conv) {
+              mbar_wait(&S.conv[stage], (conv_phase_bits >> stage) & 1);
+              conv_phase_bits ^= 1u << stage;
             }
-            umma_commit_pair(&S.empty[stage], 3);
-            if (kb == kblocks - 1) umma_commit_pair(&S.tmem_full[acc], 3);
+            tc_fence_after();
+            const uint32_t w_addr = smem_u32(S.stages + stage * GP_STAGE_BYTES);
+            const uint64_t da = umma_desc_sw128(w_addr);
+            const uint64_t db = umma_desc_sw128(w_addr + GP_W_BYTES);
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+                if constexpr (decltype(kind)::value == MMA_I8) umma_i8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+                else if constexpr (decltype(kind)::value == MMA_F8) umma_f8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+                else umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+              }
+              umma_commit_pair(&S.empty[stage], 3);
+              if (kb == kblocks - 1) umma_commit_pair(&S.tmem_full[acc], 3);
+            }
+            __syncwarp();
+            if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
           }
-          __syncwarp();
-          if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
-        }
+        };
+        if (is_i8) run_tile(std::integral_constant<int, MMA_I8>{});
+        else if (is_f8) run_tile(std::integral_constant<int, MMA_F8>{});
+        else run_tile(std::integral_constant<int, MMA_F16>{});
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -337,6 +345,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
               if (j < valid) ao[static_cast<int64_t>(c + j) * N] = static_cast<int32_t>(v[j]) >> shift;
           }
           const uint4* sap = reinterpret_cast<const uint4*>(sa_buf + c);
+          // integer accumulators (>> shift: the x16 of the in-smem w4 expansion) become floats in place; the fp32 ones of
+          // kind::f8f6f4 already are (one branch per tile, not a select per element)
+          if (!facc) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__int2float_rn(static_cast<int32_t>(v[j]) >> shift));
+          }
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const uint4 s4 = sap[g];
@@ -345,10 +359,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
             for (int j = 0; j < 4; ++j) {
               const __half2 prod = __hmul2(*reinterpret_cast<const __half2*>(&sw[j]), sb2);
               const float2 pf = __half22float2(prod);
-              // integer accumulators (>> shift: the x16 of the in-smem w4 expansion) or fp32 ones (kind::f8f6f4)
-              const float a0 = facc ? __uint_as_float(v[g * 8 + 2 * j]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j]) >> shift);
-              const float a1 = facc ? __uint_as_float(v[g * 8 + 2 * j + 1]) : __int2float_rn(static_cast<int32_t>(v[g * 8 + 2 * j + 1]) >> shift);
-              h[g * 4 + j] = pack_half2(a0 * pf.x, a1 * pf.y);
+              h[g * 4 + j] = pack_half2(__uint_as_float(v[g * 8 + 2 * j]) * pf.x, __uint_as_float(v[g * 8 + 2 * j + 1]) * pf.y);
             }
           }
         }

@@ -39,10 +39,12 @@ class MoELayer:
     def __init__(self, handle: ops.Handle, E: int, topk: int, H: int, I: int, ns: int, qlayer: QLayerConfig,
                  max_tokens: int, hadamard_down: bool = False, expert_ids: Optional[Sequence[int]] = None, seed: int = 42,
                  weights: Optional[dict] = None, device: Optional[torch.device] = None, weight_scale: float = 1.0,
-                 fuse_silu: bool = True):
+                 fuse_silu: bool = True, packed: Optional[dict] = None):
         """expert_ids: the routed experts this rank owns (expert-parallel shard); default all E.
         weights: optional {expert_idx: (W_gate_up fp16 [2I',H], W_down fp16 [H,I'])}; default U(-1,1) seed 42
-        (the reference bench's distribution, test.cu:877-915)."""
+        (the reference bench's distribution, test.cu:877-915).
+        packed: a stored layer (checkpoint.load_packed(...)[layer]): operands already in their native layouts, copied as
+        they are — no fp16 weights and no quantization pass."""
         self.h = handle
         self.E, self.topk, self.H, self.I, self.ns = E, topk, H, I, ns
         self.hadamard_down = hadamard_down
@@ -65,10 +67,27 @@ class MoELayer:
                              and all(_wonly4(qlayer.experts[str(e)].gate) and _wonly4(qlayer.experts[str(e)].down) for e in ids_all))
         gen = torch.Generator(device=self.dev).manual_seed(seed)
         ids = self.local_experts + ([E] if ns else [])
+        if packed is not None and bool(packed["gate_up_interleaved"]) != bool(self.fused_silu):
+            raise ValueError(f"stored gate_up rows are {'interleaved' if packed['gate_up_interleaved'] else 'stacked'} but this layer "
+                             f"runs {'with' if self.fused_silu else 'without'} the fused silu*mul epilogue")
         for e in ids:
             qe = qlayer.experts[str(e)]
             _check_tied(qe)
             Ie = I * ns if e == E else I
+            if packed is not None:
+                er = packed["experts"].get(str(e))
+                if er is None:
+                    raise ValueError(f"stored layer has no expert {e}")
+                if (er["gate_up"], er["down"]) != (qe.gate.qstr(), qe.down.qstr()):
+                    raise ValueError(f"expert {e}: stored as {er['gate_up']}/{er['down']}, configured {qe.gate.qstr()}/{qe.down.qstr()}")
+                t = {k: (v.to(self.dev).contiguous() if v is not None else None) for k, v in er["tensors"].items()}
+                wb_gu, wb_dn = abs(qe.gate.w_bits), abs(qe.down.w_bits)
+                if tuple(t["gu_packed"].shape) != (2 * Ie, H * wb_gu // (16 if wb_gu == 16 else 8)) or \
+                        tuple(t["dn_packed"].shape) != (H, Ie * wb_dn // (16 if wb_dn == 16 else 8)):
+                    raise ValueError(f"expert {e}: stored operand shapes {tuple(t['gu_packed'].shape)}, {tuple(t['dn_packed'].shape)} "
+                                     f"do not match H={H}, I={Ie}")
+                self.experts.append(ExpertWeights(t["gu_packed"], t["gu_scale"], t["dn_packed"], t["dn_scale"], qe.gate, qe.down))
+                continue
             if weights is not None and e in weights:
                 Wgu, Wdn = weights[e]
                 Wgu, Wdn = Wgu.to(self.dev), Wdn.to(self.dev)

@@ -37,10 +37,11 @@ class MxMoESparseBlock(torch.nn.Module):
     the (fused) shared expert, and the per-expert qconfig of the reference's JSON."""
 
     def __init__(self, handle: ops.Handle, E: int, top_k: int, H: int, I: int, ns: int, qlayer: QLayerConfig, max_tokens: int,
-                 gate_weight: torch.Tensor, weights: Dict[int, Tuple[torch.Tensor, torch.Tensor]], norm_topk_prob: bool = False,
-                 shared_gate_weight: Optional[torch.Tensor] = None, hadamard_down: bool = False):
+                 gate_weight: torch.Tensor, weights: Optional[Dict[int, Tuple[torch.Tensor, torch.Tensor]]], norm_topk_prob: bool = False,
+                 shared_gate_weight: Optional[torch.Tensor] = None, hadamard_down: bool = False, packed: Optional[dict] = None):
         super().__init__()
-        self.layer = MoELayer(handle, E, top_k, H, I, ns, qlayer, max_tokens=max_tokens, hadamard_down=hadamard_down, weights=weights)
+        self.layer = MoELayer(handle, E, top_k, H, I, ns, qlayer, max_tokens=max_tokens, hadamard_down=hadamard_down, weights=weights,
+                              packed=packed)
         dev = self.layer.dev
         self.top_k, self.norm_topk_prob = top_k, norm_topk_prob
         self.register_buffer("gate_weight", gate_weight.to(dev, torch.float16))
@@ -63,6 +64,13 @@ class MxMoESparseBlock(torch.nn.Module):
             ns = g.shape[0] // I
             weights[E] = (torch.cat([g, u], 0).half(), d.half())
         return cls(handle, E, top_k, H, I, ns, qlayer, max_tokens, gate_weight, weights, norm_topk_prob, shared_gate_weight, hadamard_down)
+
+    @classmethod
+    def from_packed(cls, handle, record: dict, max_tokens: int, gate_weight, shared_gate_weight=None, norm_topk_prob=False):
+        """record: one layer of checkpoint.load_packed(...) — experts start from their stored native-layout operands."""
+        from .checkpoint import qlayer_of
+        return cls(handle, record["E"], record["top_k"], record["H"], record["I"], record["ns"], qlayer_of(record), max_tokens, gate_weight,
+                   None, norm_topk_prob, shared_gate_weight, record["hadamard_down"], packed=record)
 
     def forward(self, hidden_states: torch.Tensor):
         shape = hidden_states.shape

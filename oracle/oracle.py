@@ -81,6 +81,9 @@ def dequant(q: np.ndarray, scale, zp, gsize: int):
 def fake_quant(t, bits, gsize, sym):
     if bits == 16:
         return t
+    if bits == BITS_E4M3:  # per-row E4M3 grid (defined below): value * scale
+        v, s = quant_e4m3(np.ascontiguousarray(t, dtype=f16))
+        return (v * s.astype(f64)).astype(f32)
     q, s, z = quant_minmax(t, bits, gsize, sym)
     return dequant(q, s, z, gsize)
 
