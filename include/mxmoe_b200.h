@@ -95,7 +95,9 @@ typedef struct MxbProblem {
  * [gate; up] order), N still counts all 2I rows, and C is fp16 [M, N/2] = silu(gate) * up with default
  * ldc = N/2.  gate and up are first rounded to fp16 exactly as the unfused GEMM would store them, then combined
  * with the arithmetic of mxb_silu_mul_quant, so the result is bit-identical to the two-step path.
- * Served by the CTA-pair kernel only: a list that is not eligible for it (see mxb_set_gemm_path) is MXB_EINVAL. */
+ * Served by the CTA-pair kernel (a list that is not eligible for it, see mxb_set_gemm_path, is MXB_EINVAL) and by the
+ * streaming weight-only kernel (decode-sized w4a16 problems; group-wise scales are interleaved along N inside every group
+ * row): there the 16-row weight slab holds 8 (gate, up) pairs and a lane gets its partner's value with one shuffle. */
 #define MXB_EPI_SILU_MUL 1
 /* Prologue fusion for the DOWN projection of a decode step: A holds the gate_up output [M, 2K] = [gate | up] (default
  * lda = 2K) and the kernel multiplies by act_fn(gate) * up, computed while the rows are staged, with the arithmetic of

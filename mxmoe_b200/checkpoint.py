@@ -66,7 +66,7 @@ def layer_record(layer) -> dict:
                            "tensors": {"gu_packed": ew.gu_packed, "gu_scale": ew.gu_scale, "dn_packed": ew.dn_packed,
                                        "dn_scale": ew.dn_scale}}
     return {"E": layer.E, "top_k": layer.topk, "H": layer.H, "I": layer.I, "ns": layer.ns, "hadamard_down": bool(layer.hadamard_down),
-            "gate_up_interleaved": bool(layer.fused_silu), "experts": experts}
+            "gate_up_interleaved": bool(layer.fused_silu or getattr(layer, "stream_epi", False)), "experts": experts}
 
 
 def save_packed(path: str, layers: Dict[int, dict], meta: Optional[dict] = None) -> int:

@@ -202,8 +202,6 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   d->a_rows = p.a_rows;
   if (p.c_row && !p.m_range) return fail(MXB_EINVAL, "c_row needs m_range (device-resident rows)");
   if (p.flags & ~(MXB_EPI_SILU_MUL | MXB_PRO_SILU_MUL)) return fail(MXB_EINVAL, "unknown problem flags 0x%x", p.flags);
-  if ((p.flags & MXB_EPI_SILU_MUL) && !paired)
-    return fail(MXB_EINVAL, "MXB_EPI_SILU_MUL is served by the CTA-pair kernel only (list not eligible, or gemm path 1)");
   d->epi_flags = p.flags;
   d->ldc = p.ldc > 0 ? p.ldc : ((p.flags & MXB_EPI_SILU_MUL) ? p.N / 2 : p.N);
   d->M = p.M;
@@ -233,6 +231,8 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   const int m_cap = p.m_range ? (p.M <= 512 ? 16 : p.M) : p.M;
   d->path = (!paired && !p.c_row && k.conv == mxb::CONV_W4_F16 && m_cap <= 64 && p.K % 128 == 0 && p.N % 16 == 0 && p.K <= mxb::w4a16_stream_max_k() &&
              p.tile_n == 0) ? 1 : 0;
+  if ((p.flags & MXB_EPI_SILU_MUL) && !paired && d->path != 1)
+    return fail(MXB_EINVAL, "MXB_EPI_SILU_MUL is served by the CTA-pair kernel and the streaming w4a16 kernel only (list not eligible, or gemm path 1)");
   if ((p.a_rows || (p.flags & MXB_PRO_SILU_MUL)) && d->path != 1)
     return fail(MXB_EINVAL, "a_rows / MXB_PRO_SILU_MUL are served by the streaming w4a16 kernel only (decode-sized weight-only problems)");
   if (k.epi == mxb::EPI_INT_GROUP) d->kb_per_group = 128 / k.k_per_block;            // int8 slabs hold 128 k

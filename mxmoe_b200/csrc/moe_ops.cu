@@ -122,6 +122,81 @@ __global__ void __launch_bounds__(PERM_THREADS) permute_scatter_kernel(const int
     __syncthreads();
   }
 }
+
+// n <= PERM_CHUNK (decode and small prefill batches): histogram, offsets and the stable scatter in ONE block and one launch
+// (the two-kernel form costs a second launch latency on a step that lasts ~150 us).  Same order as the pair above: rounds
+// of PERM_THREADS ids, inside a round by warp then lane.
+__global__ void __launch_bounds__(PERM_THREADS) permute_small_kernel(const int32_t* __restrict__ ids, int n, int k, int E,
+                                                                      int32_t* __restrict__ expert_offsets,
+                                                                      int32_t* __restrict__ src_row, int32_t* __restrict__ slot_of) {
+  extern __shared__ int32_t sh[];
+  int32_t* run = sh;       // [E] histogram, then the running output position of every expert
+  int32_t* wcnt = sh + E;  // [8][E]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int my_e[PERM_ITEMS];
+  for (int e = threadIdx.x; e < E; e += PERM_THREADS) run[e] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < PERM_ITEMS; ++it) {
+    const int i = it * PERM_THREADS + threadIdx.x;
+    int e = -1;
+    if (i < n) {
+      e = ids[i];
+      if (e < 0 || e >= E) e = -1;
+    }
+    my_e[it] = e;
+    if (e >= 0) atomicAdd(&run[e], 1);
+  }
+  __syncthreads();
+  if (warp == 0) {  // exclusive scan of the counts, 32 experts at a time
+    int carry = 0;
+    if (lane == 0) expert_offsets[0] = 0;
+    for (int b0 = 0; b0 < E; b0 += 32) {
+      const int idx = b0 + lane;
+      const int c = idx < E ? run[idx] : 0;
+      int v = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+      }
+      if (idx < E) {
+        expert_offsets[idx + 1] = v + carry;
+        run[idx] = v + carry - c;
+      }
+      carry += __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
+  const int rounds = (n + PERM_THREADS - 1) / PERM_THREADS;
+#pragma unroll
+  for (int it = 0; it < PERM_ITEMS; ++it) {
+    if (it >= rounds) break;
+    for (int j = threadIdx.x; j < 8 * E; j += PERM_THREADS) wcnt[j] = 0;
+    __syncthreads();
+    const int i = it * PERM_THREADS + threadIdx.x;
+    const int e = my_e[it];
+    const unsigned peers = __match_any_sync(0xffffffffu, e);
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    if (e >= 0 && rank == 0) wcnt[warp * E + e] = __popc(peers);
+    __syncthreads();
+    if (e >= 0) {
+      int off = run[e] + rank;
+      for (int w2 = 0; w2 < warp; ++w2) off += wcnt[w2 * E + e];
+      slot_of[i] = off;
+      src_row[off] = i / k;
+    }
+    __syncthreads();
+    if (it + 1 < rounds) {
+      for (int e2 = threadIdx.x; e2 < E; e2 += PERM_THREADS) {
+        int s2 = 0;
+#pragma unroll
+        for (int w2 = 0; w2 < 8; ++w2) s2 += wcnt[w2 * E + e2];
+        run[e2] += s2;
+      }
+      __syncthreads();
+    }
+  }
+}
 }  // namespace
 
 size_t permute_ws_bytes(int n, int E) {
@@ -135,6 +210,10 @@ cudaError_t permute_launch(const int32_t* ids, int T, int k, int E, int32_t* exp
   const int nblk = (n + PERM_CHUNK - 1) / PERM_CHUNK;
   if (nblk == 0) {
     return cudaMemsetAsync(expert_offsets, 0, sizeof(int32_t) * (E + 1), st);
+  }
+  if (nblk == 1 && E <= 1024) {
+    permute_small_kernel<<<1, PERM_THREADS, sizeof(int32_t) * 9 * E, st>>>(ids, n, k, E, expert_offsets, src_row, slot_of);
+    return cudaGetLastError();
   }
   permute_hist_kernel<<<nblk, PERM_THREADS, sizeof(int32_t) * (E + 1), st>>>(ids, n, E, ws, expert_offsets);
   permute_scatter_kernel<<<nblk, PERM_THREADS, sizeof(int32_t) * 9 * E, st>>>(ids, n, k, E, ws, expert_offsets, src_row,

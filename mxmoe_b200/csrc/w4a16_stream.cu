@@ -90,23 +90,38 @@ __device__ __forceinline__ void dequant_word(uint32_t w, uint32_t magic, __half2
   o[3] = *reinterpret_cast<uint32_t*>(&q3);
 }
 
-// cost weights of a problem's passes: every pass but the last holds 16 tokens (weight 4), the last one 4 or 3
-__device__ __forceinline__ int ws_cost(int np, int M) { return np > 0 ? 4 * (np - 1) + (M - 16 * (np - 1) > 8 ? 4 : 3) : 0; }
+// cost weights of a problem's passes: a K-stage of a pass with more than 8 tokens (two n8 MMA tiles per weight fragment)
+// takes WS_C2, one with at most 8 tokens WS_C1.  Measured per CTA (tools/ws_profile.py, c3): 1.8 us against 1.12 us per
+// stage of 16 slabs.  Every pass but the last holds 16 tokens.
+#ifndef WS_C1
+#define WS_C1 5
+#define WS_C2 8
+#endif
+__device__ __forceinline__ int ws_cost(int np, int M) { return np > 0 ? WS_C2 * (np - 1) + (M - 16 * (np - 1) > 8 ? WS_C2 : WS_C1) : 0; }
 // first item (pass-major, slab-minor) that starts at or after cost offset c inside a problem
 __device__ __forceinline__ int ws_item_of(int c, int M, int nslab, int nst) {
   const int np = (M + 15) >> 4;
-  const int full = 4 * (np - 1) * nslab * nst;  // cost of the 16-token passes before the last one
-  if (c <= full) return (c + 4 * nst - 1) / (4 * nst);
-  const int wl = (M - 16 * (np - 1) > 8 ? 4 : 3) * nst;
+  const int full = WS_C2 * (np - 1) * nslab * nst;  // cost of the 16-token passes before the last one
+  if (c <= full) return (c + WS_C2 * nst - 1) / (WS_C2 * nst);
+  const int wl = (M - 16 * (np - 1) > 8 ? WS_C2 : WS_C1) * nst;
   return (np - 1) * nslab + (c - full + wl - 1) / wl;
 }
+// The cost space is cut in units of WS_SPLIT slabs of one pass.  WS_SPLIT == WS_WARPS ("rounds": one slab for every warp)
+// keeps every entry a whole number of rounds, so no warp idles at the barrier between two entries; WS_SPLIT == 1 balances
+// the CTAs to one slab but an entry of s slabs then takes ceil(s / 16) slab times.
+#ifndef WS_SPLIT
+#define WS_SPLIT WS_WARPS
+#endif
+__device__ __forceinline__ int ws_split_units(int nslab) { return (nslab + WS_SPLIT - 1) / WS_SPLIT; }
 __device__ __forceinline__ int ws_first_slab(const WsEntry& e, int warp) { return e.sb + ((warp - e.woff) & (WS_WARPS - 1)); }
 
-// Producer cursor of one warp (only lane 0 uses it): the next stage to request.
+// Producer cursor of one warp (only lane 0 uses it): the next stage to request.  The entry's constants ride along in
+// registers, so a refill touches shared memory only when the cursor moves to another entry.
 struct WsProd {
   int i, slab, ks;
   bool live;
   int desc_p;  // problem whose weight descriptor this lane acquired last (tma_desc_acquire, ptx.cuh)
+  int p, se, nst;
 };
 
 // first entry at or after c.i this warp has a slab in
@@ -117,6 +132,9 @@ __device__ __forceinline__ void ws_prod_seek(WsProd& c, const WsEntry* ent, int 
     if (first < e.se) {
       c.slab = first;
       c.ks = 0;
+      c.p = e.p;
+      c.se = e.se;
+      c.nst = e.nst;
       c.live = true;
       return;
     }
@@ -124,13 +142,23 @@ __device__ __forceinline__ void ws_prod_seek(WsProd& c, const WsEntry* ent, int 
   c.live = false;
 }
 __device__ __forceinline__ void ws_prod_advance(WsProd& c, const WsEntry* ent, int n_ent, int warp) {
-  const WsEntry e = ent[c.i];
-  if (++c.ks < e.nst) return;
+  if (++c.ks < c.nst) return;
   c.ks = 0;
   c.slab += WS_WARPS;
-  if (c.slab < e.se) return;
+  if (c.slab < c.se) return;
   ++c.i;
   ws_prod_seek(c, ent, n_ent, warp);
+}
+// request the cursor's stage into ring slot `slot` and move on
+__device__ __forceinline__ void ws_prod_issue(WsProd& c, const DevProblem* probs, uint8_t* ring, uint64_t* full, uint32_t slot,
+                                              const WsEntry* ent, int n_ent, int warp) {
+  if (c.p != c.desc_p) {
+    tma_desc_acquire(&probs[c.p].tmB);
+    c.desc_p = c.p;
+  }
+  mbar_expect_tx(&full[slot], WS_STAGE_BYTES);
+  tma_load_2d(ring + slot * WS_STAGE_BYTES, &probs[c.p].tmB, &full[slot], c.ks * (WS_STAGE_K / 2), c.slab * WS_SLAB);
+  ws_prod_advance(c, ent, n_ent, warp);
 }
 
 struct WsProblem {  // per-entry constants of the consumer
@@ -139,15 +167,14 @@ struct WsProblem {  // per-entry constants of the consumer
   const __half* sb;
   int64_t lda, ldc;
   int N, K, gsz;
-  bool sym;
+  bool sym, epi_silu;
 };
 
 // One entry (16-token pass of one expert) for one warp: its slabs of [sb, se), K in 256-wide stages.
 template <bool TWO>
 __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& e, int mp, const uint8_t* tok, int pitchT,
                                             const uint8_t* ring, uint64_t* full, int stages, uint32_t& cslot, uint32_t& cphase, WsProd& prod,
-                                            uint32_t& pslot, const DevProblem* probs, const WsEntry* ent, int n_ent, int warp, int lane,
-                                            uint32_t magic) {
+                                            const DevProblem* probs, const WsEntry* ent, int n_ent, int warp, int lane, uint32_t magic) {
   const int g = lane >> 2, t = lane & 3;
   const int N = pb.N, K = pb.K;
   const __half2 lo_bias = __float2half2_rn(pb.sym ? 1031.f : 1024.f), nhi_bias = __float2half2_rn(pb.sym ? -71.f : -64.f);
@@ -169,31 +196,41 @@ __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& 
       if (TWO) acc1[TWO ? c : 0][q] = 0.f;
     }
   // scales of the next stage are fetched while the current one is multiplied; lane t needs the group of k = k0 + 64 t.
-  // The raw (scale, zero) words are kept as loaded and unpacked at the top of the NEXT stage.
+  // The raw (scale, zero) words are kept as loaded and unpacked at the top of the NEXT stage.  `sp` walks the lane's
+  // (scale, zero) words: + one stage (two groups) inside a slab, back to group t >> 1 of the warp's next slab after it.
   uint32_t nraw0 = 0u, nraw1 = 0u;  // asym (scale | zero << 16), sym (scale)
-  auto load_scales = [&](int slab, int ks) {
-    nraw0 = nraw1 = 0u;  // lanes past K multiply by zero
-    const int kl = ks * WS_STAGE_K + t * 64;
-    if (kl >= K) return;
-    const int64_t gi = static_cast<int64_t>(pb.gsz == K ? 0 : kl >> 7) * N + slab * WS_SLAB + g;
-    if (pb.sym) {
-      nraw0 = ld_nc_u16(pb.sb + gi);  // (not __ldg: nvcc speculates it past the bounds this lambda is called under)
-      nraw1 = ld_nc_u16(pb.sb + gi + 8);
-    } else {
-      nraw0 = ld_nc_u32(reinterpret_cast<const uint32_t*>(pb.sb) + gi);
-      nraw1 = ld_nc_u32(reinterpret_cast<const uint32_t*>(pb.sb) + gi + 8);
+  const int esh = pb.sym ? 1 : 2;   // log2 bytes per (row, group) entry
+  const int64_t st_stride = pb.gsz == K ? 0 : (static_cast<int64_t>(2 * N) << esh);
+  const int64_t slab_step = (static_cast<int64_t>(WS_WARPS * WS_SLAB) << esh) - (e.nst - 1) * st_stride;
+  const int slab0 = ws_first_slab(e, warp);
+  const uint8_t* sp = reinterpret_cast<const uint8_t*>(pb.sb) +
+                      ((static_cast<int64_t>(pb.gsz == K ? 0 : t >> 1) * N + slab0 * WS_SLAB + g) << esh);
+  int kl_next = t * 64;  // first k of the lane's share of the stage `sp` points at
+  auto load_scales = [&]() {  // (not __ldg: nvcc speculates it past the bounds this lambda is called under)
+    nraw0 = nraw1 = 0u;       // lanes past K multiply by zero
+    if (kl_next < K) {
+      if (pb.sym) {
+        nraw0 = ld_nc_u16(reinterpret_cast<const __half*>(sp));
+        nraw1 = ld_nc_u16(reinterpret_cast<const __half*>(sp) + 8);
+      } else {
+        nraw0 = ld_nc_u32(reinterpret_cast<const uint32_t*>(sp));
+        nraw1 = ld_nc_u32(reinterpret_cast<const uint32_t*>(sp) + 8);
+      }
     }
   };
-  const int slab0 = ws_first_slab(e, warp);
-  if (slab0 < e.se) load_scales(slab0, 0);
+  if (slab0 < e.se) load_scales();
   for (int slab = slab0; slab < e.se; slab += WS_WARPS) {
     const int n0 = slab * WS_SLAB;
     for (int ks = 0; ks < e.nst; ++ks) {
       const __half2 r0 = *reinterpret_cast<const __half2*>(&nraw0), r1 = *reinterpret_cast<const __half2*>(&nraw1);
       const __half2 sc0 = __half2half2(__low2half(r0)), sc1 = __half2half2(__low2half(r1));
       const __half2 zp0 = __half2half2(__high2half(r0)), zp1 = __half2half2(__high2half(r1));  // zero for symmetric codes
-      if (ks + 1 < e.nst) load_scales(slab, ks + 1);
-      else if (slab + WS_WARPS < e.se) load_scales(slab + WS_WARPS, 0);
+      {
+        const bool in_slab = ks + 1 < e.nst;
+        sp += in_slab ? st_stride : slab_step;
+        kl_next = in_slab ? kl_next + WS_STAGE_K : t * 64;
+        if (in_slab || slab + WS_WARPS < e.se) load_scales();
+      }
       mbar_wait(&full[cslot], cphase);
       const uint8_t* st = ring + cslot * WS_STAGE_BYTES;
       // lane t owns the 16-byte chunks 2t, 2t+1 of rows g and g+8 (k = k0 + 64 t .. + 64).  K % 128 == 0, so a lane's
@@ -223,18 +260,9 @@ __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& 
         }
       }
       __syncwarp();  // every lane is done reading the slot
-      if (lane == 0 && prod.live) {  // refill the slot just freed (the producer's next slot IS this one: ring order)
-        const WsEntry pe = ent[prod.i];
-        if (pe.p != prod.desc_p) {
-          tma_desc_acquire(&probs[pe.p].tmB);
-          prod.desc_p = pe.p;
-        }
-        mbar_expect_tx(&full[pslot], WS_STAGE_BYTES);
-        tma_load_2d(const_cast<uint8_t*>(ring) + pslot * WS_STAGE_BYTES, &probs[pe.p].tmB, &full[pslot], prod.ks * (WS_STAGE_K / 2),
-                    prod.slab * WS_SLAB);
-        if (++pslot == static_cast<uint32_t>(stages)) pslot = 0;
-        ws_prod_advance(prod, ent, n_ent, warp);
-      }
+      // refill the slot just freed: the producer's next slot IS this one (ring order; the slots requested so far are
+      // exactly the ones consumed so far plus the ring depth)
+      if (lane == 0 && prod.live) ws_prod_issue(prod, probs, const_cast<uint8_t*>(ring), full, cslot, ent, n_ent, warp);
       if (++cslot == static_cast<uint32_t>(stages)) {
         cslot = 0;
         cphase ^= 1u;
@@ -251,13 +279,37 @@ __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& 
                  : (acc0[0][q] + acc0[1][q]) + (acc0[2][q] + acc0[3][q]);
       }
       const int tk0 = h * 8 + 2 * t;
-      if (tk0 < mp) {
-        C[static_cast<int64_t>(tk0) * pb.ldc] = __float2half_rn(a[0]);
-        C[static_cast<int64_t>(tk0) * pb.ldc + 8] = __float2half_rn(a[2]);
-      }
-      if (tk0 + 1 < mp) {
-        C[static_cast<int64_t>(tk0 + 1) * pb.ldc] = __float2half_rn(a[1]);
-        C[static_cast<int64_t>(tk0 + 1) * pb.ldc + 8] = __float2half_rn(a[3]);
+      if (pb.epi_silu) {
+        // MXB_EPI_SILU_MUL: weight rows are interleaved (row 2i = gate_i, row 2i+1 = up_i), so lane g (even) holds gate and
+        // lane g+1 (four lanes up) the matching up values.  Both are rounded to fp16 first, like the two-step path that
+        // stores [gate | up] and applies act_fn(gate) * up on the stored values; output column (n0 + g) / 2 (+4).
+        float o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const __half mine = __float2half_rn(a[q]);
+          const __half other = __shfl_xor_sync(0xffffffffu, mine, 4);
+          o[q] = silu_mul_h(mine, other);
+        }
+        if ((g & 1) == 0) {
+          __half* Ch = pb.C + static_cast<int64_t>(e.m0) * pb.ldc + ((n0 + g) >> 1);
+          if (tk0 < mp) {
+            Ch[static_cast<int64_t>(tk0) * pb.ldc] = __float2half_rn(o[0]);
+            Ch[static_cast<int64_t>(tk0) * pb.ldc + 4] = __float2half_rn(o[2]);
+          }
+          if (tk0 + 1 < mp) {
+            Ch[static_cast<int64_t>(tk0 + 1) * pb.ldc] = __float2half_rn(o[1]);
+            Ch[static_cast<int64_t>(tk0 + 1) * pb.ldc + 4] = __float2half_rn(o[3]);
+          }
+        }
+      } else {
+        if (tk0 < mp) {
+          C[static_cast<int64_t>(tk0) * pb.ldc] = __float2half_rn(a[0]);
+          C[static_cast<int64_t>(tk0) * pb.ldc + 8] = __float2half_rn(a[2]);
+        }
+        if (tk0 + 1 < mp) {
+          C[static_cast<int64_t>(tk0 + 1) * pb.ldc] = __float2half_rn(a[1]);
+          C[static_cast<int64_t>(tk0 + 1) * pb.ldc + 8] = __float2half_rn(a[3]);
+        }
       }
     }
 #pragma unroll
@@ -270,6 +322,7 @@ __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& 
   }
 }
 
+
 // Problems are routed here by DevProblem::path == 1 (few rows per expert).  16 activation rows are resident at a time
 // (more rows re-stream the CTA's slabs, which then come from L2).
 //
@@ -279,11 +332,25 @@ __device__ __forceinline__ void ws_run_pass(const WsProblem& pb, const WsEntry& 
 // (like the tcgen05 kernels build their tile prefix) and takes the items of an equal slice of the total cost, so empty
 // experts cost nothing, an expert with 40 rows weighs three passes, K = 2816 weighs twice K = 1408, and the static
 // contiguous split stays balanced to one slab whatever the routing was.
+#ifdef WS_PROFILE
+// debug build only (make WS_PROFILE=1): per-CTA timeline of the last gate_up (slot 0, K == 2048) and down (slot 1) launch
+__device__ unsigned long long ws_prof[2][160][8];
+__device__ __forceinline__ unsigned long long ws_gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#endif
+
 __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const DevProblem* __restrict__ probs, int P, int stages,
                                                                      int tok_bytes, uint32_t magic) {
   extern __shared__ __align__(1024) uint8_t ws_smem_raw[];
   uint8_t* ws_smem = ws_smem_raw + ((1024u - (smem_u32(ws_smem_raw) & 1023u)) & 1023u);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef WS_PROFILE
+  const unsigned long long pf_t0 = ws_gtime();
+  unsigned long long pf_fill = 0, pf_ent = 0, pf_two = 0, pf_later = 0, pf_list = 0;
+#endif
   uint8_t* tok = ws_smem;
   uint8_t* ring = ws_smem + tok_bytes + warp * stages * WS_STAGE_BYTES;
   uint8_t* tail = ws_smem + tok_bytes + WS_WARPS * stages * WS_STAGE_BYTES;
@@ -301,7 +368,7 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
     if (d.m_range != nullptr) M = d.m_range[1] - d.m_range[0];
     const int np = (d.path == 1 && M > 0) ? (M + 15) >> 4 : 0;
     rows_of[i] = np > 0 ? M : 0;
-    cost_prefix[i + 1] = ws_cost(np, M) * (d.N / WS_SLAB) * ((d.K + WS_STAGE_K - 1) / WS_STAGE_K);
+    cost_prefix[i + 1] = ws_cost(np, M) * ws_split_units(d.N / WS_SLAB) * ((d.K + WS_STAGE_K - 1) / WS_STAGE_K);
   }
   __syncthreads();
   if (warp == 0) {  // inclusive scan, 32 problems per step
@@ -324,6 +391,9 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
   const int u_lo = static_cast<int>(static_cast<int64_t>(blockIdx.x) * U / gridDim.x);
   const int u_hi = static_cast<int>(static_cast<int64_t>(blockIdx.x + 1) * U / gridDim.x);
   if (u_lo >= u_hi) return;
+#ifdef WS_PROFILE
+  const unsigned long long pf_t1 = ws_gtime();
+#endif
 
   int p_next = 0;
   {  // last problem whose cost range starts at or before u_lo
@@ -335,7 +405,7 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
     }
     p_next = lo;
   }
-  uint32_t cslot = 0, cphase = 0, pslot = 0;
+  uint32_t cslot = 0, cphase = 0;
 
   for (;;) {
     __syncthreads();  // the previous list is fully consumed
@@ -347,13 +417,14 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
       while (n < WS_MAX_ENT && !last) {
         const int p = base + lane;
         const bool inr = p < P && cost_prefix[min(p, P)] < u_hi;
-        int ia = 0, ib = 0, nslab = 1, nst = 1, M = 0, row0 = 0;
+        int ia = 0, ib = 0, nslab = 1, nslab_real = 1, nst = 1, M = 0, row0 = 0;  // nslab: split units per pass (WS_SPLIT slabs each)
         if (inr) {
           const int pre = cost_prefix[p], pre1 = cost_prefix[p + 1];
           if (pre1 > pre) {
             const DevProblem& d = probs[p];
             nst = (d.K + WS_STAGE_K - 1) / WS_STAGE_K;
-            nslab = d.N / WS_SLAB;
+            nslab_real = d.N / WS_SLAB;
+            nslab = ws_split_units(nslab_real);
             M = rows_of[p];
             if (d.m_range != nullptr) row0 = d.m_range[0];
             // (DevProblem::c_row is not honoured here: api.cu keeps such problems off this path)
@@ -364,7 +435,10 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
         const bool has = ib > ia;
         const int pa = ia / nslab, pb = has ? (ib - 1) / nslab : pa;
         const int cnt = has ? pb - pa + 1 : 0;
-        int pos = cnt, sl = ib - ia;  // exclusive scans of the entry counts and the slab counts
+        int nsl = 0;  // slabs of this problem's entries
+        for (int ps = pa; has && ps <= pb; ++ps)
+          nsl += min((ps == pb ? ib - pb * nslab : nslab) * WS_SPLIT, nslab_real) - (ps == pa ? ia - pa * nslab : 0) * WS_SPLIT;
+        int pos = cnt, sl = nsl;  // exclusive scans of the entry counts and the slab counts
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
           const int u = __shfl_up_sync(0xffffffffu, pos, o), v = __shfl_up_sync(0xffffffffu, sl, o);
@@ -375,7 +449,7 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
         }
         const int tot_cnt = __shfl_sync(0xffffffffu, pos, 31), tot_sl = __shfl_sync(0xffffffffu, sl, 31);
         pos = n + pos - cnt;
-        sl = slabs_before + sl - (ib - ia);
+        sl = slabs_before + sl - nsl;
         const bool fits = pos + cnt <= WS_MAX_ENT;
         if (has && fits) {
           for (int ps = pa; ps <= pb; ++ps) {
@@ -384,8 +458,8 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
             e.m0 = ps * 16;
             e.M = M;
             e.row0 = row0;
-            e.sb = ps == pa ? ia - pa * nslab : 0;
-            e.se = ps == pb ? ib - pb * nslab : nslab;
+            e.sb = (ps == pa ? ia - pa * nslab : 0) * WS_SPLIT;
+            e.se = min((ps == pb ? ib - pb * nslab : nslab) * WS_SPLIT, nslab_real);
             e.woff = sl & (WS_WARPS - 1);
             e.nst = nst;
             sl += e.se - e.sb;
@@ -417,19 +491,13 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
     p_next = ctl[1];
 
     // producer: request the first `stages` boxes of this list
-    WsProd prod = {0, 0, 0, false, -1};
+    WsProd prod = {0, 0, 0, false, -1, 0, 0, 0};
     if (lane == 0) {
       ws_prod_seek(prod, ent, n_ent, warp);
+      uint32_t pslot = cslot;  // the ring is empty between two lists
       for (int s = 0; s < stages && prod.live; ++s) {
-        const WsEntry pe = ent[prod.i];
-        if (pe.p != prod.desc_p) {
-          tma_desc_acquire(&probs[pe.p].tmB);
-          prod.desc_p = pe.p;
-        }
-        mbar_expect_tx(&full[pslot], WS_STAGE_BYTES);
-        tma_load_2d(ring + pslot * WS_STAGE_BYTES, &probs[pe.p].tmB, &full[pslot], prod.ks * (WS_STAGE_K / 2), prod.slab * WS_SLAB);
+        ws_prod_issue(prod, probs, ring, full, pslot, ent, n_ent, warp);
         if (++pslot == static_cast<uint32_t>(stages)) pslot = 0;
-        ws_prod_advance(prod, ent, n_ent, warp);
       }
     }
 
@@ -443,6 +511,7 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
       pb.ldc = d.ldc;
       const int32_t* a_rows = d.a_rows;
       const bool pro_silu = (d.epi_flags & 2) != 0;  // MXB_PRO_SILU_MUL: A = [gate | up], rows become silu(gate) * up
+      pb.epi_silu = (d.epi_flags & 1) != 0;          // MXB_EPI_SILU_MUL: interleaved gate/up weight rows, C = act_fn(gate) * up
       pb.A = static_cast<const __half*>(d.A_ptr) + (a_rows ? 0 : static_cast<int64_t>(e.row0) * pb.lda);
       pb.C = d.C + static_cast<int64_t>(e.row0) * pb.ldc;
       pb.sb = d.scale_b;
@@ -453,6 +522,9 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
       const int mp = min(16, e.M - e.m0);
       const bool two = mp > 8;
       __syncthreads();  // previous entry done with the token rows
+#ifdef WS_PROFILE
+      const unsigned long long pf_f0 = ws_gtime();
+#endif
       const int fill_rows = two ? 16 : 8;  // rows mp..fill_rows-1 are zero; rows 8..15 are never read when mp <= 8
       const int upr = K >> 3;              // 16-byte units per row
       for (int idx = threadIdx.x; idx < fill_rows * upr; idx += WS_WARPS * 32) {
@@ -480,11 +552,34 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
       }
       cp_async_wait_all();
       __syncthreads();  // token rows visible to every warp
-      if (two) ws_run_pass<true>(pb, e, mp, tok, pitchT, ring, full, stages, cslot, cphase, prod, pslot, probs, ent, n_ent, warp, lane, magic);
-      else ws_run_pass<false>(pb, e, mp, tok, pitchT, ring, full, stages, cslot, cphase, prod, pslot, probs, ent, n_ent, warp, lane, magic);
+#ifdef WS_PROFILE
+      pf_fill += ws_gtime() - pf_f0;
+      pf_ent += 1;
+      pf_two += two ? (e.se - e.sb) * e.nst : 0;
+      pf_later += e.m0 > 0 ? (e.se - e.sb) * e.nst : 0;
+#endif
+      if (two) ws_run_pass<true>(pb, e, mp, tok, pitchT, ring, full, stages, cslot, cphase, prod, probs, ent, n_ent, warp, lane, magic);
+      else ws_run_pass<false>(pb, e, mp, tok, pitchT, ring, full, stages, cslot, cphase, prod, probs, ent, n_ent, warp, lane, magic);
     }
+#ifdef WS_PROFILE
+    pf_list += 1;
+#endif
     if (last_list) break;
   }
+#ifdef WS_PROFILE
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long* o = ws_prof[probs[0].K == 2048 ? 0 : 1][blockIdx.x];
+    o[0] = pf_t0;
+    o[1] = pf_t1 - pf_t0;
+    o[2] = ws_gtime() - pf_t0;
+    o[3] = pf_fill;
+    o[4] = pf_ent;
+    o[5] = pf_two;
+    o[6] = pf_later;
+    o[7] = static_cast<unsigned long long>(u_hi - u_lo);
+  }
+#endif
 }
 
 int ws_smem_bytes(int K, int P, int* stages_out, int* tok_bytes_out) {
@@ -516,6 +611,12 @@ void w4a16_stream_launch(const DevProblem* probs, int P, int est_units, int max_
     w4a16_stream_kernel<<<grid, WS_WARPS * 32, smem, st>>>(probs + off, n, stages, tokb, 0x64006400u);
   }
 }
+
+#ifdef WS_PROFILE
+extern "C" int mxb_debug_ws_profile(unsigned long long* out) {
+  return static_cast<int>(cudaMemcpyFromSymbol(out, ws_prof, sizeof(ws_prof)));
+}
+#endif
 
 int w4a16_stream_rows_per_group() { return WS_WARPS * WS_SLAB; }
 int w4a16_stream_max_k() { return 4096; }

@@ -405,12 +405,13 @@ class EPMoELayer(MoELayer):
         return self._last_seg.reshape(self.W, self.EL).sum(0).tolist()
 
     def launches_per_step(self) -> int:
+        perm1 = 1 if self.T_local * self.topk <= 2048 else 0  # permute_small_kernel: one launch instead of two
         if self.push:  # permute (2), counts, plan, quant+push, GroupGEMM x2, (rotate+)quant, combine; shared: quant, GEMM x2, quant
-            n = 9 + (4 if self.ns and self.overlap else (2 if self.ns else 0))
+            n = 9 - perm1 + (4 if self.ns and self.overlap else (2 if self.ns else 0))
             if self.fused_silu:
                 n -= (1 if self.h_direct else 0) + (1 if self.ns and self.sh_direct else 0)
             return n
-        n = 8 + (2 if self.ns else 0) + (0 if self.sender_quant else 1)
+        n = 8 - perm1 + (2 if self.ns else 0) + (0 if self.sender_quant else 1)
         if self.fused_silu:
             n -= (1 if self.h_direct else 0) + (1 if self.ns and self.sh_direct else 0)
         return n

@@ -9,6 +9,7 @@ marshalled once and re-used through the plan cache, shared experts ride in the s
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
 
@@ -27,6 +28,16 @@ class ExpertWeights:
     dn_scale: Optional[torch.Tensor]
     q_gu: QLinearConfig
     q_dn: QLinearConfig
+
+
+def _interleave_group_major(s: Optional[torch.Tensor], N: int, asym: bool) -> Optional[torch.Tensor]:
+    """Scales in the group-major layout of permute_scale ([K/g, N], asym: [K/g, N, 2] = (scale, zero); stored flat): columns
+    [gate_0.. | up_0..] -> (gate_0, up_0, gate_1, up_1, ...) inside every group row, like the weight rows."""
+    if s is None:
+        return None
+    c = 2 if asym else 1
+    assert s.numel() % (N * c) == 0
+    return s.view(-1, 2, N // 2, c).transpose(1, 2).contiguous().view(s.shape)
 
 
 def _check_tied(q: QExpertConfig):
@@ -65,9 +76,13 @@ class MoELayer:
         self.stream_fused = (expert_ids is None and max_tokens <= 64 and max_tokens * topk <= 512 and H % 128 == 0 and I % 128 == 0
                              and not hadamard_down
                              and all(_wonly4(qlayer.experts[str(e)].gate) and _wonly4(qlayer.experts[str(e)].down) for e in ids_all))
+        # ... and produces act_fn(gate) * up in the gate_up epilogue instead (MXB_EPI_SILU_MUL over interleaved gate/up rows):
+        # every element of h is then computed once, not once per CTA that stages the row for the down projection.
+        # MXB_STREAM_EPI=0 keeps the staging form (MXB_PRO_SILU_MUL over stacked rows).
+        self.stream_epi = self.stream_fused and os.environ.get("MXB_STREAM_EPI", "1") != "0"
         gen = torch.Generator(device=self.dev).manual_seed(seed)
         ids = self.local_experts + ([E] if ns else [])
-        if packed is not None and bool(packed["gate_up_interleaved"]) != bool(self.fused_silu):
+        if packed is not None and bool(packed["gate_up_interleaved"]) != bool(self.fused_silu or self.stream_epi):
             raise ValueError(f"stored gate_up rows are {'interleaved' if packed['gate_up_interleaved'] else 'stacked'} but this layer "
                              f"runs {'with' if self.fused_silu else 'without'} the fused silu*mul epilogue")
         for e in ids:
@@ -98,6 +113,9 @@ class MoELayer:
             if self.fused_silu:  # rows (gate_i, up_i) adjacent: the epilogue pairs neighbouring TMEM lanes
                 gu_p = handle.interleave_gate_up(gu_p)
                 gu_s = handle.interleave_gate_up(gu_s) if gu_s is not None else None
+            elif self.stream_epi:  # same row order for the streaming kernel; its scales are group-major [K/g, N(, 2)]
+                gu_p = handle.interleave_gate_up(gu_p)
+                gu_s = _interleave_group_major(gu_s, 2 * Ie, not qe.gate.w_sym)
             self.experts.append(ExpertWeights(gu_p, gu_s, *self._pack(Wdn, qe.down), qe.gate, qe.down))
             del Wgu, Wdn
         self._alloc(max_tokens)
@@ -167,7 +185,7 @@ class MoELayer:
             mr = self.offs[i:i + 2]
             if self.stream_fused:  # gate_up is built per input buffer (A = x itself, _finalize_problems); down reads [gate | up]
                 dn.append(self._problem(ew.q_dn, None, self.gu_out, None, ew.dn_packed, ew.dn_scale, self.dn_out, R, H, I, mr,
-                                        flags=ops.PRO_SILU_MUL))
+                                        flags=0 if self.stream_epi else ops.PRO_SILU_MUL))
                 continue
             gu.append(self._problem(ew.q_gu, self.x_q8, self.x_f16, self.x_sc, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * I, H, mr,
                                     flags=ops.EPI_SILU_MUL if self.fused_silu else 0))
@@ -190,14 +208,16 @@ class MoELayer:
         gu, dn = list(self._gu_routed), list(self._dn_routed)
         if self.stream_fused:
             R = self.max_tokens * self.topk
+            epi = ops.EPI_SILU_MUL if self.stream_epi else 0  # gu_out then holds h = act_fn(gate) * up as dense [R, I] rows
             gu = [self._problem(ew.q_gu, None, x, None, ew.gu_packed, ew.gu_scale, self.gu_out, R, 2 * self.I, self.H,
-                                self.offs[i:i + 2], a_rows=self.src) for i, ew in enumerate(self.experts[:self.EL])]
+                                self.offs[i:i + 2], a_rows=self.src, flags=epi) for i, ew in enumerate(self.experts[:self.EL])]
         if self.ns and self.stream_fused:
             s = self.experts[-1]
             Is = self.I * self.ns
-            gu.append(self._problem(s.q_gu, None, x, None, s.gu_packed, s.gu_scale, self.s_gu, T, 2 * Is, self.H, None))
+            gu.append(self._problem(s.q_gu, None, x, None, s.gu_packed, s.gu_scale, self.s_gu, T, 2 * Is, self.H, None,
+                                    flags=ops.EPI_SILU_MUL if self.stream_epi else 0))
             dn.append(self._problem(s.q_dn, None, self.s_gu, None, s.dn_packed, s.dn_scale, self.s_dn, T, self.H, Is, None,
-                                    flags=ops.PRO_SILU_MUL))
+                                    flags=0 if self.stream_epi else ops.PRO_SILU_MUL))
         elif self.ns:
             s = self.experts[-1]
             Is = self.I * self.ns
@@ -302,11 +322,13 @@ class MoELayer:
         o = self.offs.cpu().tolist()
         return [o[i + 1] - o[i] for i in range(self.EL)]
 
-    def launches_per_step(self) -> int:
-        # permute (2) + act-quant (1 [+1 shared]) + GroupGEMM (1) + silu*mul+quant (1 [+1 shared]) + GroupGEMM (1) + combine (1)
+    def launches_per_step(self, T: Optional[int] = None) -> int:
+        # permute (2; 1 when the T*k ids fit one block: permute_small_kernel) + act-quant (1 [+1 shared]) + GroupGEMM (1)
+        # + silu*mul+quant (1 [+1 shared]) + GroupGEMM (1) + combine (1)
+        perm = 1 if (self.max_tokens if T is None else T) * self.topk <= 2048 else 2
         if self.stream_fused:
-            return 5  # permute (2) + GroupGEMM (gather fused) + GroupGEMM (silu*mul fused) + combine
-        n = 7 + (2 if self.ns else 0)
+            return perm + 3  # permute + GroupGEMM (gather fused) + GroupGEMM (silu*mul fused) + combine
+        n = 5 + perm + (2 if self.ns else 0)
         if self.fused_silu:
             n -= (1 if self.h_direct else 0) + (1 if self.ns and self.sh_direct else 0)
         return n

@@ -395,6 +395,28 @@ def test_w4a16_streaming_kernel(H, gsize, sym, M, N, K):
     check([p], [ref], [None])
 
 
+@pytest.mark.parametrize("gsize,sym", [(128, False), (128, True), (-1, False)])
+@pytest.mark.parametrize("M", [1, 6, 8, 13, 16, 40])
+def test_w4a16_streaming_fused_silu_mul_is_bit_identical_to_two_steps(H, gsize, sym, M):
+    """MXB_EPI_SILU_MUL on the streaming kernel: interleaved gate/up weight rows and scales, C = act_fn(gate) * up [M, I].
+    Must equal, bit for bit, the two-step form (GroupGEMM -> [M, 2I] -> mxb_silu_mul_quant in fp16 mode), whose GEMM is
+    checked against the oracle."""
+    from mxmoe_b200 import ops
+    from mxmoe_b200.layer import _interleave_group_major
+    rng = np.random.default_rng(M * 7 + (gsize & 3) + sym)
+    I, K = 264, 1408  # 33 slabs of 16 interleaved rows: a partial last round
+    p, ref, _ = make_problem(ops, rng, M, 2 * I, K, 4, 16, gsize, sym)
+    H.group_gemm([p])
+    check([p], [ref], [None])
+    _, two_step, _ = H.silu_mul_quant(p.C, M, None, [(16, -1)])
+    Cf = torch.full((max(M, 1), I), float("nan"), dtype=torch.float16, device="cuda")
+    pf = ops.Problem(p.A, H.interleave_gate_up(p.B), Cf, M, 2 * I, K, 4, 16, gsize, sym,
+                     scale_b=_interleave_group_major(p.scale_b, 2 * I, not sym), flags=ops.EPI_SILU_MUL)
+    H.group_gemm([pf])
+    torch.cuda.synchronize()
+    assert torch.equal(Cf[:M].view(torch.int16), two_step[:M].view(torch.int16)), "fused silu*mul differs from the two-step path"
+
+
 def test_w4a16_streaming_many_experts_device_m(H):
     """Decode-shaped list: 40 experts sharing one activation buffer with DEVICE-resident row ranges (0..16 rows each,
     several empty) -> one streaming launch; every expert against the oracle."""

@@ -137,7 +137,7 @@ def test_decode_layer_stream_fused_is_bit_identical_and_graphable(gsize, sym):
     dx, dids, dw = torch.from_numpy(x).cuda(), torch.from_numpy(ids).cuda(), torch.from_numpy(w).cuda()
     h = ops.Handle(0)
     fused = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw)
-    assert fused.stream_fused and fused.launches_per_step() == 5
+    assert fused.stream_fused and fused.launches_per_step() == 4
     plain = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw)
     plain.stream_fused = False
     plain._build_problems()
