@@ -78,8 +78,8 @@ class MoELayer:
                              and all(_wonly4(qlayer.experts[str(e)].gate) and _wonly4(qlayer.experts[str(e)].down) for e in ids_all))
         # ... and produces act_fn(gate) * up in the gate_up epilogue instead (MXB_EPI_SILU_MUL over interleaved gate/up rows):
         # every element of h is then computed once, not once per CTA that stages the row for the down projection.
-        # MXB_STREAM_EPI=0 keeps the staging form (MXB_PRO_SILU_MUL over stacked rows).
-        self.stream_epi = self.stream_fused and os.environ.get("MXB_STREAM_EPI", "1") != "0"
+        # fuse_silu=False or MXB_STREAM_EPI=0 keeps the staging form (MXB_PRO_SILU_MUL over stacked rows).
+        self.stream_epi = self.stream_fused and fuse_silu and os.environ.get("MXB_STREAM_EPI", "1") != "0"
         gen = torch.Generator(device=self.dev).manual_seed(seed)
         ids = self.local_experts + ([E] if ns else [])
         if packed is not None and bool(packed["gate_up_interleaved"]) != bool(self.fused_silu or self.stream_epi):

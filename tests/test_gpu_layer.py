@@ -107,8 +107,8 @@ def test_fused_silu_epilogue_layer_is_bit_identical(hadamard):
 @pytest.mark.parametrize("gsize,sym", [(128, False), (-1, True)])
 def test_decode_layer_stream_fused_is_bit_identical_and_graphable(gsize, sym):
     """Decode step of a weight-only 4-bit layer (the c3 shape scaled down, 24 tokens, one expert left empty, a shared
-    expert with ns = 2): the streaming kernel with the token gather (MxbProblem.a_rows) and act_fn(gate)*up
-    (MXB_PRO_SILU_MUL) folded into its row staging against (a) the same layer run as separate
+    expert with ns = 2): the streaming kernel with the token gather (MxbProblem.a_rows) folded into its row staging and
+    act_fn(gate)*up in the gate_up epilogue (MXB_EPI_SILU_MUL) or in the down staging (MXB_PRO_SILU_MUL) against (a) the same layer run as separate
     quant_act / GroupGEMM / silu_mul_quant / GroupGEMM launches: identical bits; (b) the oracle within the w4a16
     tolerance; (c) its own CUDA-graph replay on new inputs: identical bits."""
     from mxmoe_b200 import ops
@@ -138,14 +138,19 @@ def test_decode_layer_stream_fused_is_bit_identical_and_graphable(gsize, sym):
     h = ops.Handle(0)
     fused = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw)
     assert fused.stream_fused and fused.launches_per_step() == 4
-    plain = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw)
+    assert fused.stream_epi  # act_fn(gate)*up in the gate_up epilogue (MXB_EPI_SILU_MUL over interleaved rows)
+    staged = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw, fuse_silu=False)  # ... while staging the down rows
+    assert staged.stream_fused and not staged.stream_epi
+    plain = MoELayer(h, E, k, Hd, I, ns, ql, max_tokens=T, weights=tw, fuse_silu=False)
     plain.stream_fused = False
     plain._build_problems()
     y_f = fused.forward(dx, dids, dw).clone()
+    y_s = staged.forward(dx, dids, dw).clone()
     y_p = plain.forward(dx, dids, dw).clone()
     torch.cuda.synchronize()
     assert torch.isfinite(y_f.float()).all()
     assert torch.equal(y_f.view(torch.int16), y_p.view(torch.int16))
+    assert torch.equal(y_s.view(torch.int16), y_p.view(torch.int16))
     qc = [((4, 16, gsize, sym), (4, 16, gsize, sym))] * (E + 1)
     ref = O.moe_layer(x, ids, w, weights, qc, E, False, (weights[E][0], weights[E][1], qc[E][0], qc[E][1]))
     o, r = y_f.cpu().numpy().astype(np.float64), ref.astype(np.float64)
