@@ -307,8 +307,12 @@ def main():
         if s["ns"]:
             io_bytes += T * (s["H"] * act_bytes + 3 * s["I"] * s["ns"] * 2 + s["H"] * 2)
         ach = (w_bytes + io_bytes) * steps / (ms_gemm * 1e-3) / 1e9
-        roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": None,
-                "kernel": ("gg_pair_kernel" if layer.fused_silu else "gg_persistent_kernel + w4a16_stream_kernel") + " (gate_up + down launches of one step)",
+        # dram read + write of the two launches from one `ncu --set full` capture (profiles/ncu_w4a16_stream_r01.txt)
+        traffic = 320.7e6 if (args.workload == "c3" and W == 1 and not args.bs) else None
+        stream = getattr(layer, "stream_fused", False)
+        roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"], "traffic": traffic,
+                "kernel": ("gg_pair_kernel" if layer.fused_silu else "w4a16_stream_kernel" if stream else
+                           "gg_persistent_kernel + w4a16_stream_kernel") + " (gate_up + down launches of one step)",
                 "peak_source": pk["src"] + " copy bandwidth",
                 "algorithmic": f"{w_bytes} B packed weights of the active experts + {io_bytes} B activations in/out per step",
                 "ms_per_launch_pair": ms_gemm / steps}

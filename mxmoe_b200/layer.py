@@ -30,14 +30,15 @@ class ExpertWeights:
     q_dn: QLinearConfig
 
 
-def _interleave_group_major(s: Optional[torch.Tensor], N: int, asym: bool) -> Optional[torch.Tensor]:
+def _interleave_group_major(s: Optional[torch.Tensor], N: int, asym: bool, inverse: bool = False) -> Optional[torch.Tensor]:
     """Scales in the group-major layout of permute_scale ([K/g, N], asym: [K/g, N, 2] = (scale, zero); stored flat): columns
-    [gate_0.. | up_0..] -> (gate_0, up_0, gate_1, up_1, ...) inside every group row, like the weight rows."""
+    [gate_0.. | up_0..] -> (gate_0, up_0, gate_1, up_1, ...) inside every group row, like the weight rows (inverse: back)."""
     if s is None:
         return None
     c = 2 if asym else 1
     assert s.numel() % (N * c) == 0
-    return s.view(-1, 2, N // 2, c).transpose(1, 2).contiguous().view(s.shape)
+    v = s.view(-1, N // 2, 2, c) if inverse else s.view(-1, 2, N // 2, c)
+    return v.transpose(1, 2).contiguous().view(s.shape)
 
 
 def _check_tied(q: QExpertConfig):
@@ -82,7 +83,16 @@ class MoELayer:
         self.stream_epi = self.stream_fused and fuse_silu and os.environ.get("MXB_STREAM_EPI", "1") != "0"
         gen = torch.Generator(device=self.dev).manual_seed(seed)
         ids = self.local_experts + ([E] if ns else [])
+        # Stored rows against this layer's row order.  Only the decode form depends on the batch size, so only there the loader
+        # adapts: stacked rows keep the staging form; interleaved rows of a decode record are put back in [gate; up] order for a
+        # layer that is too large for the streaming kernel.  Everything else is a configuration error.
+        relayout = False
         if packed is not None and bool(packed["gate_up_interleaved"]) != bool(self.fused_silu or self.stream_epi):
+            if self.stream_epi:
+                self.stream_epi = False
+            elif fuse_silu and not self.fused_silu and all(_wonly4(qlayer.experts[str(e)].gate) for e in ids_all):
+                relayout = True
+        if packed is not None and not relayout and bool(packed["gate_up_interleaved"]) != bool(self.fused_silu or self.stream_epi):
             raise ValueError(f"stored gate_up rows are {'interleaved' if packed['gate_up_interleaved'] else 'stacked'} but this layer "
                              f"runs {'with' if self.fused_silu else 'without'} the fused silu*mul epilogue")
         for e in ids:
@@ -96,6 +106,9 @@ class MoELayer:
                 if (er["gate_up"], er["down"]) != (qe.gate.qstr(), qe.down.qstr()):
                     raise ValueError(f"expert {e}: stored as {er['gate_up']}/{er['down']}, configured {qe.gate.qstr()}/{qe.down.qstr()}")
                 t = {k: (v.to(self.dev).contiguous() if v is not None else None) for k, v in er["tensors"].items()}
+                if relayout:
+                    t["gu_packed"] = t["gu_packed"].view(Ie, 2, -1).transpose(0, 1).reshape(2 * Ie, -1).contiguous()
+                    t["gu_scale"] = _interleave_group_major(t["gu_scale"], 2 * Ie, not qe.gate.w_sym, inverse=True)
                 wb_gu, wb_dn = abs(qe.gate.w_bits), abs(qe.down.w_bits)
                 if tuple(t["gu_packed"].shape) != (2 * Ie, H * wb_gu // (16 if wb_gu == 16 else 8)) or \
                         tuple(t["dn_packed"].shape) != (H, Ie * wb_dn // (16 if wb_dn == 16 else 8)):

@@ -39,7 +39,8 @@ def test_saved_layer_reloads_bit_identical(tmp_path, kinds, T):
     if all(c["w_bits"] < 16 for c in kinds):
         assert nbytes < dense * 0.6
     rec = CK.load_packed(p, device="cuda")[7]
-    assert rec["gate_up_interleaved"] == L.fused_silu
+    assert rec["gate_up_interleaved"] == (L.fused_silu or L.stream_epi)
+    assert L.stream_epi == (T == 24)  # the decode step keeps gate/up rows interleaved for the streaming kernel's epilogue
     L2 = CK.layer_from_record(ops.Handle(0), rec, max_tokens=T)
     rng = np.random.default_rng(3)
     x = torch.from_numpy((rng.random((T, H)) * 2 - 1).astype(np.float16)).cuda()
@@ -50,6 +51,19 @@ def test_saved_layer_reloads_bit_identical(tmp_path, kinds, T):
     torch.cuda.synchronize()
     assert torch.isfinite(y1.float()).all() and float(y1.float().abs().max()) > 0
     assert torch.equal(y1, y2)
+    if L.stream_epi:
+        # a decode record (interleaved rows for the streaming kernel's epilogue) also loads into a layer that is too large for
+        # that kernel: the loader puts the rows back in [gate; up] order
+        Tb = 200
+        big = MoELayer(h, E, k, H, I, ns, ql, max_tokens=Tb, weight_scale=0.1, seed=5)
+        big2 = CK.layer_from_record(ops.Handle(0), rec, max_tokens=Tb)
+        assert not big.stream_fused and not big2.stream_fused
+        xb = torch.from_numpy((rng.random((Tb, H)) * 2 - 1).astype(np.float16)).cuda()
+        idb = torch.from_numpy(np.stack([rng.permutation(E)[:k] for _ in range(Tb)]).astype(np.int32)).cuda()
+        wb = torch.from_numpy(rng.random((Tb, k)).astype(np.float32)).cuda()
+        yb, yb2 = big.forward(xb, idb, wb).clone(), big2.forward(xb, idb, wb).clone()
+        torch.cuda.synchronize()
+        assert torch.equal(yb, yb2)
 
 
 def test_layout_mismatch_is_refused(tmp_path):
