@@ -359,16 +359,24 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
   int* ctl = reinterpret_cast<int*>(ent + WS_MAX_ENT);  // [0] entries in the list, [1] next problem, [2] list is the last one
   int* cost_prefix = ctl + 4;                           // [P+1]
   int* rows_of = cost_prefix + P + 1;                     // [P] rows of every problem (as read for the prefix)
+  int* row0_of = rows_of + P;                             // [P] first row (m_range[0]); the list build reads no global memory
+  int* shape_of = row0_of + P;                            // [P] slabs << 8 | K-stages
   if (lane < stages) mbar_init(&full[lane], 1);
   fence_mbar_init();
 
   for (int i = threadIdx.x; i < P; i += WS_WARPS * 32) {
     const DevProblem& d = probs[i];
-    int M = d.M;
-    if (d.m_range != nullptr) M = d.m_range[1] - d.m_range[0];
+    int M = d.M, r0 = 0;
+    if (d.m_range != nullptr) {
+      r0 = d.m_range[0];
+      M = d.m_range[1] - r0;
+    }
     const int np = (d.path == 1 && M > 0) ? (M + 15) >> 4 : 0;
+    const int nst = (d.K + WS_STAGE_K - 1) / WS_STAGE_K;  // <= 16 (K <= 4096)
     rows_of[i] = np > 0 ? M : 0;
-    cost_prefix[i + 1] = ws_cost(np, M) * ws_split_units(d.N / WS_SLAB) * ((d.K + WS_STAGE_K - 1) / WS_STAGE_K);
+    row0_of[i] = r0;
+    shape_of[i] = ((d.N / WS_SLAB) << 8) | nst;
+    cost_prefix[i + 1] = ws_cost(np, M) * ws_split_units(d.N / WS_SLAB) * nst;
   }
   __syncthreads();
   if (warp == 0) {  // inclusive scan, 32 problems per step
@@ -421,12 +429,11 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
         if (inr) {
           const int pre = cost_prefix[p], pre1 = cost_prefix[p + 1];
           if (pre1 > pre) {
-            const DevProblem& d = probs[p];
-            nst = (d.K + WS_STAGE_K - 1) / WS_STAGE_K;
-            nslab_real = d.N / WS_SLAB;
+            nst = shape_of[p] & 0xff;
+            nslab_real = shape_of[p] >> 8;
             nslab = ws_split_units(nslab_real);
             M = rows_of[p];
-            if (d.m_range != nullptr) row0 = d.m_range[0];
+            row0 = row0_of[p];
             // (DevProblem::c_row is not honoured here: api.cu keeps such problems off this path)
             ia = ws_item_of(max(u_lo, pre) - pre, M, nslab, nst);
             ib = ws_item_of(min(u_hi, pre1) - pre, M, nslab, nst);
@@ -584,7 +591,7 @@ __global__ void __launch_bounds__(WS_WARPS * 32, 1) w4a16_stream_kernel(const De
 
 int ws_smem_bytes(int K, int P, int* stages_out, int* tok_bytes_out) {
   const int tokb = (16 * (K * 2 + 64) + 1023) & ~1023;  // the ring is 1024-byte aligned (swizzle atom)
-  const int fixed = WS_WARPS * WS_MAX_STAGES * 8 + WS_MAX_ENT * static_cast<int>(sizeof(WsEntry)) + 16 + (2 * P + 1) * 4 + 64;
+  const int fixed = WS_WARPS * WS_MAX_STAGES * 8 + WS_MAX_ENT * static_cast<int>(sizeof(WsEntry)) + 16 + (4 * P + 1) * 4 + 64;
   int stages = (227 * 1024 - 1024 - tokb - fixed) / (WS_WARPS * WS_STAGE_BYTES);
   if (stages > WS_MAX_STAGES) stages = WS_MAX_STAGES;
   *stages_out = stages;
