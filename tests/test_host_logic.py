@@ -83,3 +83,20 @@ def test_run_mxmoe_gg_cli_dry_run(tmp_path):
     wl = json.load(open(os.path.join(root, "out", "workloads", "qwen2_moe-wiki2-8192-qcfg.json")))
     assert wl["num_tokens"] == 8192 and len(wl["layer-11"]["gate_up"]) == 61
     assert {p["w_bits"] for p in wl["layer-11"]["down"]} == {4, 8}
+
+
+def test_gate_up_scale_interleave_roundtrip():
+    """Group-major scales ([K/g, N] / [K/g, N, 2], ref quantize.cuh:299-315 permute_scale) follow the gate/up row interleave of
+    MXB_EPI_SILU_MUL inside every group row; the inverse restores the stacked order (decode records loaded into large layers)."""
+    import torch
+    from mxmoe_b200.layer import _interleave_group_major as il
+    G, N = 3, 8
+    for asym in (False, True):
+        c = 2 if asym else 1
+        s = torch.arange(G * N * c, dtype=torch.float32).half()
+        o = il(s, N, asym)
+        v, w = s.view(G, N, c), o.view(G, N, c)
+        for i in range(N // 2):
+            assert torch.equal(w[:, 2 * i], v[:, i]) and torch.equal(w[:, 2 * i + 1], v[:, N // 2 + i])
+        assert torch.equal(il(o, N, asym, inverse=True), s)
+    assert il(None, N, False) is None
