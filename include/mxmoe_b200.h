@@ -87,6 +87,9 @@ typedef struct MxbProblem {
   const int32_t* a_rows;              /* optional: DEVICE int32 per row of the problem's row range = the row of A to read (the
                                          token gather of gg_permute_inp, ref_bind.cu:47-64, folded into the operand load).  A is
                                          then the un-permuted [T, K] buffer.  Streaming (decode) path only. */
+  int64_t lds_a;                      /* fp16 elements per row of scale_a; 0 = dense (1 for per-token scales, K/128 for gsize 128).
+                                         A buffer shared by per-token and group-wise experts (the layer allocates [rows, K/128] as
+                                         soon as one expert of the launch is g128) is read at this pitch by every problem. */
 } MxbProblem;
 
 /* Epilogue fusion of the step that follows the gate_up GEMM in the reference pipeline (silu_mul_then_quant,
@@ -125,6 +128,9 @@ int mxb_destroy(mxb_handle_t h);
 const char* mxb_last_error(void);
 int mxb_sm_count(mxb_handle_t h);
 const char* mxb_version(void);
+/* sizeof of an ABI struct as this library was compiled (0 MxbProblem, 1 MxbActQ, 2 MxbRowDest, 3 MxbTileChoice; else -1):
+ * lets a binding (ctypes, cgo, JNI) check its mirror of the layout before the first call. */
+int mxb_struct_size(int which);
 /* Which GroupGEMM kernel serves mxb_group_gemm*: 0 (default) = chosen per problem list — the CTA-pair kernel
  * (tcgen05 cta_group::2, 256 weight rows x <=256 tokens per tile) when every problem is fp16 / w8a8 / w4a4 with
  * g-1 scales and no explicit tile_n, else the single-CTA kernel; 1 = always the single-CTA kernel; 2 = the

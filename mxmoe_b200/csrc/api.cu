@@ -220,6 +220,10 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   d->gsize = p.gsize;
   d->sym = p.sym;
   d->scale_a_ld = (k.epi == mxb::EPI_INT_GROUP) ? p.K / 128 : 1;
+  if (p.lds_a > 0) {  // scale rows at the caller's pitch (a buffer shared by per-token and group-wise experts)
+    if (p.lds_a < d->scale_a_ld || p.lds_a > (1 << 20)) return fail(MXB_EINVAL, "lds_a=%lld below the %d scales a row holds", (long long)p.lds_a, d->scale_a_ld);
+    d->scale_a_ld = (int32_t)p.lds_a;
+  }
   d->A_ptr = p.A;
   d->B_ptr = p.B;
   d->lda = lda;
@@ -484,6 +488,16 @@ int mxb_destroy(mxb_handle_t c) {
 }
 
 int mxb_sm_count(mxb_handle_t c) { return c ? c->sm_count : 0; }
+
+int mxb_struct_size(int which) {
+  switch (which) {
+    case 0: return (int)sizeof(MxbProblem);
+    case 1: return (int)sizeof(MxbActQ);
+    case 2: return (int)sizeof(MxbRowDest);
+    case 3: return (int)sizeof(MxbTileChoice);
+    default: return -1;
+  }
+}
 
 int mxb_set_sm_limit(mxb_handle_t c, int sms) {
   if (!c) return fail(MXB_EINVAL, "null handle");

@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(GG_THREADS, 1) gg_persistent_kernel(const DevP
 
       if (epi != EPI_INT_GROUP) {
         __half sa = __float2half(1.f);
-        if (epi == EPI_INT_ROWCOL && row_ok) sa = d.scale_a[grow];
+        if (epi == EPI_INT_ROWCOL && row_ok) sa = d.scale_a[static_cast<int64_t>(grow) * d.scale_a_ld];
         mbar_wait(&S.tmem_full[acc], acc_phase);
         tc_fence_after();
         for (int c = 0; c < bn; c += 32) {

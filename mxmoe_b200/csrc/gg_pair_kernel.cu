@@ -318,8 +318,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       __half2 sb2 = __float2half2_rn(1.f);
       if (epi == EPI_INT_ROWCOL) {
         // stage the tile's per-token scales (each thread 2 of them), fetch this lane's per-channel scale
-        const __half* sa = d.scale_a + grow0;
-        sa_buf[et] = et < t.nt ? sa[et] : __float2half(0.f);
+        const int64_t sald = d.scale_a_ld;  // 1, or the pitch of a scale buffer shared with group-wise experts
+        const __half* sa = d.scale_a + grow0 * sald;
+        sa_buf[et] = et < t.nt ? sa[et * sald] : __float2half(0.f);
         if (n_ok) sb2 = __half2half2(d.scale_b[n]);
       }
       // every tile, also the unscaled ones: keeps the eight warps within one tile of each other, which is what makes

@@ -187,7 +187,7 @@ class MoELayer:
         A = A_f16 if q.a_bits >= 16 else A_q8
         return ops.Problem(A, B, C, rows, N, K, q.w_bits, q.a_bits, q.w_gsize, q.w_sym if q.w_bits < 16 else True,
                            scale_a=sc if q.a_bits < 16 else None, scale_b=sb, m_range=m_range, flags=flags, c_row=c_row,
-                           a_rows=a_rows)
+                           a_rows=a_rows, lds_a=int(sc.shape[1]) if (q.a_bits < 16 and sc is not None and sc.dim() == 2) else 0)
 
     def _build_problems(self):
         """Marshal the two problem lists once; M of every routed expert is read on the device from self.offs."""

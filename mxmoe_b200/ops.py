@@ -40,6 +40,7 @@ class MxbProblem(C.Structure):
         ("a_bits", C.c_int32), ("w_bits", C.c_int32), ("gsize", C.c_int32), ("sym", C.c_int32),
         ("tile_n", C.c_int32), ("flags", C.c_int32),
         ("c_row", C.c_void_p), ("a_rows", C.c_void_p),
+        ("lds_a", C.c_int64),
     ]
 
 
@@ -64,6 +65,7 @@ EXPORTS = [
     ("mxb_last_error", C.c_char_p, []),
     ("mxb_sm_count", _I, [_P]),
     ("mxb_version", C.c_char_p, []),
+    ("mxb_struct_size", _I, [_I]),
     ("mxb_set_gemm_path", _I, [_P, _I]),
     ("mxb_set_sm_limit", _I, [_P, _I]),
     ("mxb_group_gemm", _I, [_P, C.POINTER(MxbProblem), _I, _P]),
@@ -101,6 +103,10 @@ def load_library(path: str = _LIB_PATH):
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    for which, st in enumerate((MxbProblem, MxbActQ, MxbRowDest, MxbTileChoice)):
+        if lib.mxb_struct_size(which) != C.sizeof(st):
+            raise MxbError(f"{path}: sizeof({st.__name__}) is {lib.mxb_struct_size(which)} in the library, {C.sizeof(st)} in the ctypes "
+                           "mirror — rebuild the library (make -C mxmoe_b200/csrc)")
     _lib = lib
     return lib
 
@@ -135,11 +141,12 @@ class Problem:
     flags: int = 0  # EPI_SILU_MUL: B rows interleaved (gate_i, up_i), C = silu(gate)*up [M, N/2]
     c_row: Optional[torch.Tensor] = None  # device int32: first row of the problem in C when it is not m_range[0]
     a_rows: Optional[torch.Tensor] = None  # device int32 per sorted row: the row of A to read (streaming path)
+    lds_a: int = 0  # fp16 elements per row of scale_a; 0 = dense (1 per-token, K/128 group-wise)
 
     def to_c(self) -> MxbProblem:
         return MxbProblem(_ptr(self.A), _ptr(self.B), _ptr(self.scale_a), _ptr(self.scale_b), _ptr(self.C),
                           _ptr(self.m_range), self.lda, self.ldc, self.M, self.N, self.K, self.a_bits, self.w_bits,
-                          self.gsize, 1 if self.sym else 0, self.tile_n, self.flags, _ptr(self.c_row), _ptr(self.a_rows))
+                          self.gsize, 1 if self.sym else 0, self.tile_n, self.flags, _ptr(self.c_row), _ptr(self.a_rows), self.lds_a)
 
 
 class Handle:

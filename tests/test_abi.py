@@ -41,10 +41,13 @@ def test_ctypes_mirror_matches_header(lib):
     from mxmoe_b200 import ops
     names = sorted(n for n, _, _ in ops.EXPORTS)
     assert names == declared_symbols()
-    assert ctypes.sizeof(ops.MxbProblem) == 6 * 8 + 2 * 8 + 9 * 4 + 4 + 16  # 6 pointers, 2 int64, 9 int32, padding, c_row, a_rows
+    assert ctypes.sizeof(ops.MxbProblem) == 6 * 8 + 2 * 8 + 9 * 4 + 4 + 16 + 8  # 6 pointers, 2 int64, 9 int32, padding, c_row, a_rows, lds_a
     assert ctypes.sizeof(ops.MxbRowDest) == 32
     assert ctypes.sizeof(ops.MxbActQ) == 8
     assert ctypes.sizeof(ops.MxbTileChoice) == 24
+    # ... and against the structs as the library was compiled
+    for which, st in enumerate((ops.MxbProblem, ops.MxbActQ, ops.MxbRowDest, ops.MxbTileChoice)):
+        assert lib.mxb_struct_size(which) == ctypes.sizeof(st)
 
 
 def test_pure_host_entry_points(lib):

@@ -75,6 +75,18 @@ def test_layer_mixed_with_hadamard():
     assert np.mean(np.abs(o - r) > 2e-3 * scale) < 0.01
 
 
+def test_layer_mixes_group_and_per_token_activation_scales():
+    """w4a4_g128 next to w8a8_g-1 / w4a4_g-1 experts in ONE layer (the reference solver's own strategy list has this mix,
+    bits_solver.py:471).  The activation scale buffer is then [rows, K/128] for every expert and the per-token problems
+    must read their scale at that pitch (MxbProblem.lds_a), not at stride 1.  Same bar as the integer test."""
+    cfgs = [(lin(4, 4, 128), lin(4, 4, 128)), (lin(8, 8), lin(8, 8)), (lin(4, 4), lin(4, 4, 128)), (lin(8, 8), lin(4, 4))]
+    out, ref = run_case(E=8, k=2, Hd=256, I=256, ns=0, T=96, cfgs=cfgs, hadamard=False, seed=5)
+    o, r = out.astype(np.float64), ref.astype(np.float64)
+    assert np.isfinite(o).all()
+    assert np.mean(o != r) < 5e-3
+    assert np.abs(o - r).max() <= 1e-2 * np.abs(r).max()
+
+
 @pytest.mark.parametrize("hadamard", [False, True])
 def test_fused_silu_epilogue_layer_is_bit_identical(hadamard):
     """The layer with silu(gate)*up fused into the gate_up GroupGEMM epilogue (CTA-pair kernel, MXB_EPI_SILU_MUL)
