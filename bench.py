@@ -114,23 +114,46 @@ def cpu_sample_problems(model, layer, q, n=3):
     from mxmoe_b200 import config as C
     s = C.MODEL_SHAPES[model]
     ql = qlayer_for(model, layer, q)
+    t = lambda c: (c.w_bits, c.a_bits, c.w_gsize, c.w_sym if c.w_bits < 16 else True)
     out = []
     for e in range(n):
         qe = ql.experts[str(e)]
-        t = lambda c: (c.w_bits, c.a_bits, c.w_gsize, c.w_sym if c.w_bits < 16 else True)
         out.append((e, t(qe.gate), t(qe.down)))
-    return s, out
+    shared = None
+    if s["ns"]:
+        qe = ql.experts[str(s["E"])]
+        shared = (t(qe.gate), t(qe.gate))  # the shared down problem takes the gate config (gen_workload.py:101)
+    return s, out, shared
+
+
+def cpu_sample(wl, n_experts):
+    """The reference's CPU torch path (oracle/cpu_path.py) on a bounded sample that keeps the workload's mix: n routed
+    experts at the mean row count, the shared expert on the matching share of tokens (rows_routed / top-k), the online
+    Hadamard when the workload has it."""
+    s, sample, shared = cpu_sample_problems(wl["model"], wl["layer"], wl["q"], n_experts)
+    M = max(1, wl["bs"] * s["topk"] // s["E"])
+    probs = [(M, s["H"], s["I"], qg, qd) for (_, qg, qd) in sample]
+    Ms = 0
+    if shared is not None:
+        Ms = max(1, n_experts * M // s["topk"])
+        probs.append((Ms, s["H"], s["I"] * s["ns"], shared[0], shared[1]))
+    what = (f"{n_experts} routed experts of the workload (M={M} each)"
+            + (f" + the shared expert on {Ms} tokens (the routed:shared ratio of the full step)" if Ms else "")
+            + ": per-token fake-quant hook (torch port of quant.py:40-106)"
+            + (" + online Hadamard hook (torch matmul_hadU)" if wl["hadamard"] else "")
+            + " + F.linear, gate_up -> silu*mul -> down, torch fp32 on all host threads")
+    return probs, what
 
 
 def run_cpu(wl, n_experts, repeats):
+    """cpu_baseline of the default arm: median of `repeats` passes + the same sample without the activation hooks."""
     from oracle import cpu_path
-    s, sample = cpu_sample_problems(wl["model"], wl["layer"], wl["q"], n_experts)
-    M = max(1, wl["bs"] * s["topk"] // s["E"])
-    probs = [(M, s["H"], s["I"], qg, qd) for (_, qg, qd) in sample]
-    ops, sec, threads = cpu_path.time_sample(probs, repeats=repeats)
-    return dict(value=ops / sec / 1e12, unit="TOPS", cores=threads, kind="port",
-                sample=f"{n_experts} routed experts of the workload (M={M} each, gate_up+silu*mul+down with on-the-fly "
-                       f"fake-quant), torch fp32 CPU path, best of {repeats}"), ops, sec
+    probs, what = cpu_sample(wl, n_experts)
+    ops, sec, threads = cpu_path.time_sample(probs, repeats=repeats, hadamard=wl["hadamard"])
+    base = dict(value=ops / sec / 1e12, unit="TOPS", cores=threads, kind="port", sample=what + f", median of {repeats}")
+    ops2, sec2, _ = cpu_path.time_sample(probs, repeats=repeats, matmul_only=True)
+    base["matmul_only_value"] = ops2 / sec2 / 1e12  # what the host cores do on the matmuls alone
+    return base
 
 
 def main():
@@ -151,25 +174,28 @@ def main():
     W = max(1, args.gpus)
     steps, warmup = args.steps, max(3, args.warmup)
     cfg = {"workload": wl["name"], "bs_per_gpu": wl["bs"], "routing": "synthetic top-k (fixture expert popularity), seed 0",
-           "weights": "U(-1,1)*0.05 fp16, seed 42, quantized+packed on device", "parallelism": f"ep{W}" if W > 1 else "single",
+           "weights": ("U(-1,1)*0.05 fp16, seed 42, fake-quantized offline (host)" if args.impl == "reference" else
+                       "U(-1,1)*0.05 fp16, seed 42, quantized+packed on device"), "parallelism": f"ep{W}" if W > 1 else "single",
            "l2": "working set per step (packed weights + activations, >0.9 GB) exceeds the 126 MB L2; no explicit flush"}
 
     if args.impl == "reference":
         if rank != 0:
             return
-        # the reference's CPU torch path on this box's host cores, bounded sample per step
-        base, ops, sec = None, 0, 0.0
-        t_tot = 0.0
-        for i in range(warmup + steps):
-            b, ops, sec = run_cpu(wl, 2, 1)
-            if i >= warmup:
-                t_tot += sec
-                base = b
-            if i >= warmup and t_tot > 120:
-                steps = i - warmup + 1
+        # the reference's CPU torch path on this box's host cores: every step is one pass over a bounded sample
+        from oracle import cpu_path
+        probs, what = cpu_sample(wl, 3)
+        smp = cpu_path.CpuSample(probs, hadamard=wl["hadamard"])
+        for _ in range(warmup):
+            smp.run()
+        times = []
+        for _ in range(steps):
+            times.append(smp.run())
+            if sum(times) > 150:  # keep the arm within a few minutes on a slow host
                 break
-        v = ops * steps / t_tot / 1e12
-        base["value"] = v
+        steps = len(times)
+        t_tot = sum(times)
+        v = smp.ops * steps / t_tot / 1e12
+        base = dict(value=v, unit="TOPS", cores=smp.threads, kind="port", sample=what + f", {steps} timed passes")
         print(json.dumps({"impl": "reference", "metric": "MoE-layer GroupGEMM TOPS", "value": v, "unit": "TOPS", "n_gpus": W,
                           "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * t_tot / steps, "higher_is_better": True,
                           "scaling": "weak", "vs_baseline": None, "dtype": "f32 (host) over int8/int4 grids", "data": "synthetic",
@@ -337,7 +363,7 @@ def main():
             "roofline": roof}
     if rank == 0:
         if not args.no_cpu and W == 1:
-            line["cpu_baseline"], _, _ = run_cpu(wl, 3, 3)
+            line["cpu_baseline"] = run_cpu(wl, 3, 3)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -163,7 +163,7 @@ def runtime_cost(model: str, layer_workload: Dict[str, list], strategies: Sequen
             for p in lst:
                 M, N, K = p["shape"]
                 probs.append(ops.MxbProblem(None, None, None, None, None, None, 0, 0, max(int(M), 1), int(N), int(K), q.a_bits, q.w_bits,
-                                            q.w_gsize, 1 if (q.w_sym or q.w_bits >= 16) else 0, 0, 0, None, None))
+                                            q.w_gsize, 1 if (q.w_sym or q.w_bits >= 16) else 0, 0, 0, None, None, 0))
         arr = (ops.MxbProblem * len(probs))(*probs)
         out = (ops.MxbTileChoice * len(probs))()
         rc = lib.mxb_select_tiles(handle.h if handle is not None else None, arr, len(probs), out)
@@ -222,6 +222,39 @@ def solve_model(model: str, strategies: Sequence[str], wbits: float, batch: int,
     return out
 
 
+def tile_config_for(model: str, qcfg: dict, batch: int, trace_kind: str = "fixture") -> Dict[str, str]:
+    """The `_tile_cfg.json` the reference writes next to the qconfig (export_qconfig, bits_solver.py:30,67-68):
+    {layer: repr of one TileConfig per strategy used in the layer}.  Here the tile comes from `mxb_select_tiles` for the
+    layer's mean routed gate_up problem under that strategy; PATH / QCFG are this library's additions to the repr
+    (config.tile_for / tile_hint read them back; run_mxmoe_gg.py --tile_config consumes the file)."""
+    import ctypes  # noqa: F401
+
+    from . import ops
+    lib = ops.load_library()
+    s = C.MODEL_SHAPES[model]
+    M = max(1, batch * s["topk"] // s["E"])
+    out = {}
+    for li, layer in qcfg.items():
+        if li == "LT":
+            continue
+        used = sorted({C.QLinearConfig.from_dict(b[n]).qstr() for b in layer["experts"].values() for n in BLOCKS})
+        reps = []
+        for qs in used:
+            q = C.QLinearConfig.from_qstr(qs)
+            pr = ops.MxbProblem(None, None, None, None, None, None, 0, 0, M, 2 * s["I"], s["H"], q.a_bits, q.w_bits, q.w_gsize,
+                                1 if (q.w_sym or q.w_bits >= 16) else 0, 0, 0, None, None, 0)
+            arr = (ops.MxbProblem * 1)(pr)
+            ch = (ops.MxbTileChoice * 1)()
+            if lib.mxb_select_tiles(None, arr, 1, ch) != 0:
+                raise ops.MxbError(f"mxb_select_tiles failed for {qs}: {lib.mxb_last_error().decode()}")
+            t = ch[0]
+            mma = ("UMMA_F16" if q.a_bits >= 16 else "UMMA_F8F6F4" if q.w_bits == C.BITS_E4M3 else "UMMA_I8") + ("_2CTA" if t.path == 2 else "")
+            reps.append(f"TileConfig(BM={t.tile_m}, BN={t.tile_n}, BK={t.tile_k}, WM=1, WN=1, WK=1, STAGE={t.stages}, SPLITK=-1, "
+                        f"MMA='{mma}', PATH={t.path}, QCFG='{qs}')")
+        out[str(li)] = "(" + ", ".join(reps) + ("," if len(reps) == 1 else "") + ")"
+    return out
+
+
 def average_wbits(qcfg: dict, model: str) -> float:
     s = C.MODEL_SHAPES[model]
     sizes = [1.0] * s["E"] + ([float(s["ns"])] if s["ns"] else [])
@@ -257,6 +290,9 @@ def main(argv=None):
     if a.out:
         json.dump(q, open(a.out, "w"))
         print("wrote", a.out)
+        tpath = a.out[:-5] + "_tile_cfg.json" if a.out.endswith(".json") else a.out + "_tile_cfg.json"
+        json.dump(tile_config_for(a.model, q, a.batch), open(tpath, "w"))
+        print("wrote", tpath)
 
 
 if __name__ == "__main__":

@@ -174,6 +174,41 @@ def load_tile_config(path: str) -> Dict[str, List[dict]]:
     return out
 
 
+def tile_for(tiles: Dict[str, List[dict]], qstr: str, layer: int, qcfg_list: List[str]) -> Optional[dict]:
+    """The tile_config entry that applies to problems of kind `qstr` in `layer`, for both schemas:
+    {qcfg: [TileConfig...]} (compose_kernel.py:87-91: the first entry is the one the generator instantiates) and
+    {layer: (TileConfig per strategy)} (bits_solver.py:30,67-68: by this library's export matched on its QCFG field,
+    by the reference's export positionally in the sorted strategy list)."""
+    if not tiles:
+        return None
+    if qstr in tiles:
+        return tiles[qstr][0] if tiles[qstr] else None
+    ent = tiles.get(str(layer))
+    if not ent:
+        return None
+    for t in ent:
+        if t.get("QCFG") == qstr:
+            return t
+    order = sorted(qcfg_list)
+    if qstr in order and order.index(qstr) < len(ent) and "QCFG" not in ent[order.index(qstr)]:
+        return ent[order.index(qstr)]
+    return None
+
+
+def tile_hint(tile: Optional[dict]) -> int:
+    """MxbProblem.tile_n for a tile_config entry.  On sm_100 the MMA atom is fixed by the hardware, so an entry selects the
+    kernel path and the UMMA N: entries written by this library carry PATH (2 = CTA-pair kernel, 1 = streaming kernel:
+    both choose the token extent per tile themselves -> 0; 0 = single-CTA kernel at UMMA N = BN); an entry of the
+    reference (sm_80/89 tiles, no PATH) is honoured at the granularity that exists here: its BN becomes the UMMA N of the
+    single-CTA kernel, rounded down to 32/64/128/256."""
+    if not tile or "BN" not in tile:
+        return 0
+    if tile.get("PATH", 0) in (1, 2):
+        return 0
+    bn = int(tile["BN"])
+    return 256 if bn >= 256 else 128 if bn >= 128 else 64 if bn >= 64 else 32
+
+
 MODEL_ID_TO_LAYERS = {"qwen2_moe": 24, "qwen2_moe_57b": 28, "ds2": 27, "mixtral": 32}
 
 # E routed experts, top-k, shared-expert multiple ns, hidden H, moe intermediate I (SURVEY §8 shape table)

@@ -90,8 +90,8 @@ struct mxb_context {
 
 namespace {
 
-constexpr int kMaxPlans = 64;
-constexpr int kMaxTables = 64;
+constexpr int kMaxPlans = 512;  // a 28-layer stack keeps 4 lists per layer alive on one handle
+constexpr int kMaxTables = 256;
 
 // Encode a 2-D row-major tensor [rows, inner_elems] with a [box_rows, box_inner] box.
 int encode_2d(mxb_context* c, CUtensorMap* tm, CUtensorMapDataType dt, int elsize, const void* base, uint64_t inner_elems,

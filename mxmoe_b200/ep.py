@@ -1,26 +1,17 @@
-"""Expert-parallel MoE layer over the GPUs of one node (one process per GPU, torch.distributed / NCCL).
+"""Expert-parallel MoE layer over the GPUs of one node (one process per GPU; torch.distributed for the rendezvous).
 
 The reference has no multi-GPU path at all (no NCCL/MPI anywhere); this is the partitioning
-BASELINE.json's north_star asks for: rank r owns a contiguous slice of the routed experts (weights never
-move), every rank brings its own tokens, and the only exchanges are the token DISPATCH (rows already
-quantized to int8 containers + fp16 scales by the sender when the experts allow it: half the NVLink bytes
-of fp16 rows) and the COMBINE of the fp16 down-projection rows, both `all_to_all_single` with per-peer split
-sizes.  Shared experts are replicated and run on the local tokens in the same GroupGEMM launches.
+BASELINE.json's north_star asks for: rank r owns a slice of the routed experts (weights never move), every rank
+brings its own tokens, and the only exchanges are the token DISPATCH (rows already quantized to int8 containers +
+fp16 scales by the sender when the experts allow it: half the NVLink bytes of fp16 rows) and the COMBINE of the fp16
+down-projection rows.  The shared expert is replicated and runs on the local tokens.
 
 Received rows arrive grouped by (source rank, local expert).  They are NOT regrouped: every (source, expert)
 segment becomes its own GroupGEMM problem pointing at the same expert weights, with its row range read on the
 device (MxbProblem.m_range), so dispatch -> GEMM needs no gather pass.
 
-The one host synchronisation per step is the read-back of the [W, E] count matrix needed for the split sizes.
-
-Overlap: the replicated shared expert depends on the local tokens only, so its chain (act-quant, gate_up GEMM,
-Hadamard+quant, down GEMM) runs on a side stream through a second handle whose persistent kernels leave
-`comm_sms` SMs free (mxb_set_sm_limit): its gate_up half sits under the count read-back and the dispatch
-all-to-all, its down half under the combine all-to-all.  NCCL's kernels and the persistent GEMM cannot share an
-SM (the GEMM CTA owns the register file), hence the SM split rather than plain stream concurrency.
-
-exchange="push" (default when torch symmetric memory rendezvous works): no NCCL and no host read-back on the data
-path.  Receive buffers, the return buffer and the [W, E] count matrix live in symmetric memory (every rank maps every
+exchange="push" (the design; default on NCCL process groups): no NCCL and no host read-back on the data path.
+Receive buffers, the return buffer and the [W, E] count matrix live in torch symmetric memory (every rank maps every
 peer's allocation over NVLink), and the exchange is done by the kernels that produce the data:
   counts     mxb_ep_push_counts writes this rank's counts into every peer's matrix            -> barrier
   plan       mxb_ep_plan derives, ON THE DEVICE, the destination of every expert's rows, the layout of what this rank
@@ -30,12 +21,22 @@ peer's allocation over NVLink), and the exchange is done by the kernels that pro
   combine    the down GroupGEMM's epilogue stores each segment into the SOURCE rank's return buffer (MxbProblem.C =
              peer pointer, c_row = its first row there)                                        -> barrier
   then the local top-k weighted sum.  Capacity is the worst case (W * T * k rows), so routing can never overflow a peer.
+
+exchange="nccl" (the baseline the push path is measured against, and the path of gloo/CPU host-logic tests):
+`all_to_all_single` of the quantized rows + scales and of the fp16 down rows with per-peer split sizes; its one host
+synchronisation per step is the read-back of the [W, E] count matrix the split sizes come from.
+
+Overlap: the replicated shared expert depends on the local tokens only, so its chain (act-quant, gate_up GEMM,
+Hadamard+quant, down GEMM) runs on a side stream through a second handle whose persistent kernels leave `comm_sms`
+SMs free (mxb_set_sm_limit) for the dispatch kernel (push) or NCCL's kernels: a persistent GEMM CTA owns its SM's
+register file, hence the SM split rather than plain stream concurrency.
 """
 from __future__ import annotations
 
 from typing import List, Optional, Sequence, Tuple
 
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -85,10 +86,13 @@ class EPMoELayer(MoELayer):
     def __init__(self, handle: ops.Handle, E: int, topk: int, H: int, I: int, ns: int, qlayer: QLayerConfig, max_tokens: int,
                  hadamard_down: bool = False, capacity: float = 2.0, seed: int = 42, weight_scale: float = 1.0,
                  group: Optional[dist.ProcessGroup] = None, weights: Optional[dict] = None, overlap_shared: bool = True,
-                 comm_sms: int = 20, exchange: str = "auto", expert_order: Optional[Sequence[int]] = None):
+                 comm_sms: int = 20, exchange: str = "auto", expert_order: Optional[Sequence[int]] = None,
+                 share: Optional["EPMoELayer"] = None):
         """expert_order: placement of the experts (default 0..E-1): rank r owns expert_order[bounds[r]:bounds[r+1]]
         (balanced_expert_order builds one from a popularity profile).  Internally experts are relabelled by their position
-        in the order, so every kernel still sees contiguous slices; topk_ids keep the caller's numbering."""
+        in the order, so every kernel still sees contiguous slices; topk_ids keep the caller's numbering.
+        share: an earlier layer of the same stack (same shapes, same world): activation, exchange (symmetric-memory) and routing
+        buffers, the side stream and the side handle are re-used — the layers of a stack run one after the other."""
         self.group = group
         self.W = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
@@ -109,48 +113,50 @@ class EPMoELayer(MoELayer):
         self.sender_quant = all(a < 16 for a, _ in self.q_all)
         self.any_g128 = any(g == 128 for a, g in self.q_all if a < 16)
         cap_tokens = (self.cap_rows + topk - 1) // topk
-        # every rank draws the weights of ALL experts from the same stream position so that the model is the same
-        # regardless of W: seed is offset per expert inside MoELayer by construction order -> use a per-rank seed
+        # MoELayer seeds its generator per expert, so the model is the same whatever W is (and the replicated shared expert
+        # has the same weights on every rank)
+        self._scale_cols = H // 128 if self.any_g128 else 1
         super().__init__(handle, E, topk, H, I, ns, qlayer, max_tokens=cap_tokens, hadamard_down=hadamard_down,
-                         expert_ids=mine, seed=seed + 1000 * self.rank, weight_scale=weight_scale, weights=weights)
+                         expert_ids=mine, seed=seed, weight_scale=weight_scale, weights=weights, share=share)
         d = self.dev
         relabel = np.empty(E, dtype=np.int32)
         relabel[np.asarray(order)] = np.arange(E, dtype=np.int32)
         self.relabel = None if order == list(range(E)) else torch.from_numpy(relabel).to(d)
         R = max_tokens * topk
-        cols = H // 128 if self.any_g128 else 1
-        if self.sender_quant and self.x_sc.shape[1] != cols:  # receive buffer must match the senders' scale width
-            self.x_sc = torch.empty(self.x_sc.shape[0], cols, dtype=torch.float16, device=d)
+        cols = self._scale_cols
+        B = self._buf
+        if not self.push and self.sender_quant and self.x_sc.shape[1] != cols:  # receive buffer must match the senders' scale width
+            self.x_sc = B("x_sc_recv", (self.x_sc.shape[0], cols), torch.float16)
         nccl = not self.push  # staging buffers of the NCCL exchange
-        self.send_q8 = torch.empty(R, H, dtype=torch.int8, device=d) if (nccl and self.sender_quant) else None
-        self.send_sc = torch.empty(R, cols, dtype=torch.float16, device=d) if (nccl and self.sender_quant) else None
-        self.send_f16 = None if (self.sender_quant or not nccl) else torch.empty(R, H, dtype=torch.float16, device=d)
-        self.recv_f16 = None if (self.sender_quant or not nccl) else torch.empty(self.cap_rows, H, dtype=torch.float16, device=d)
-        self.seg_offs = torch.zeros(self.W * self.EL + 1, dtype=torch.int32, device=d)
+        self.send_q8 = B("send_q8", (R, H), torch.int8) if (nccl and self.sender_quant) else None
+        self.send_sc = B("send_sc", (R, cols), torch.float16) if (nccl and self.sender_quant) else None
+        self.send_f16 = None if (self.sender_quant or not nccl) else B("send_f16", (R, H), torch.float16)
+        self.recv_f16 = None if (self.sender_quant or not nccl) else B("recv_f16", (self.cap_rows, H), torch.float16)
+        self.seg_offs = B("seg_offs", (self.W * self.EL + 1,), torch.int32, zero=True)
         if self.push:
             self._setup_push(R, H, cols)
         else:
-            self.back = torch.empty(R, H, dtype=torch.float16, device=d)
-            self.counts_all = torch.zeros(self.W, E, dtype=torch.int32, device=d)
+            self.back = B("back", (R, H), torch.float16)
+            self.counts_all = B("counts_all", (self.W, E), torch.int32, zero=True)
         self._last_seg = None
         self._build_segment_problems()
-        # the shared expert's chain on a side stream, on a handle whose persistent kernels leave SMs to NCCL
-        import os
+        # the shared expert's chain on a side stream, on a handle whose persistent kernels leave SMs to the exchange
         if os.environ.get("MXB_EP_OVERLAP") is not None:
             overlap_shared = os.environ["MXB_EP_OVERLAP"] != "0"
         comm_sms = int(os.environ.get("MXB_EP_COMM_SMS", comm_sms))
         self.tail_wait = os.environ.get("MXB_EP_TAIL_WAIT", "0") != "0"
         self.overlap = bool(overlap_shared and ns and self.W > 1)
-        if self.overlap:
+        if self.overlap and share is not None and getattr(share, "overlap", False):
+            self.h_side, self.side = share.h_side, share.side
+            self.ev_in, self.ev_mid, self.ev_gu, self.ev_side = share.ev_in, share.ev_mid, share.ev_gu, share.ev_side
+        elif self.overlap:
             self.h_side = ops.Handle(handle.device)
             self.h_side.set_sm_limit(handle.sm_count - comm_sms)
             self.side = torch.cuda.Stream(d)
             self.ev_in, self.ev_mid, self.ev_gu, self.ev_side = (torch.cuda.Event() for _ in range(4))
         # the dispatch kernel is NVLink-bound: when the shared expert runs beside it, it keeps to the SMs left free
-        import os
         self.push_ctas = int(os.environ.get("MXB_EP_PUSH_CTAS", comm_sms * 8 if self.overlap else 0))
         # MXB_EP_TIMING=1: CUDA events at the phase boundaries of forward(), read with timing_report()
-        import os
         self._timing = os.environ.get("MXB_EP_TIMING", "0") == "1"
         self._marks = []
 
@@ -176,36 +182,52 @@ class EPMoELayer(MoELayer):
     def _build_problems(self):
         self._T_built = None
 
-    def _setup_push(self, R: int, H: int, cols: int):
-        """Symmetric-memory buffers + peer views (collective: every rank calls it in the same order)."""
+    def _symm(self, name: str, shape, dtype):
+        """A symmetric-memory buffer + its peer views (collective: every rank calls it in the same order); pooled like
+        MoELayer._buf so that the layers of a stack rendezvous once."""
         import torch.distributed._symmetric_memory as symm
-        d, W, E = self.dev, self.W, self.E
-        gname = (self.group or dist.group.WORLD).group_name
-        self._symm_handles = []
-
-        def shared(shape, dtype):
-            t = symm.empty(shape, dtype=dtype, device=d)
+        key = ("symm", name, tuple(int(v) for v in shape), dtype)
+        ent = self._pool.get(key)
+        if ent is None:
+            gname = (self.group or dist.group.WORLD).group_name
+            t = symm.empty(key[2], dtype=dtype, device=self.dev)
             t.zero_()
             hdl = symm.rendezvous(t, gname)
-            self._symm_handles.append(hdl)
-            peers = [t if p == self.rank else hdl.get_buffer(p, tuple(shape), dtype) for p in range(W)]
-            return t, peers, hdl
+            peers = [t if p == self.rank else hdl.get_buffer(p, key[2], dtype) for p in range(self.W)]
+            ent = (t, peers, hdl)
+            self._pool[key] = ent
+        return ent
 
-        cap = self.cap_rows
+    def _alloc(self, T: int):
+        """push exchange: the receive buffers of the gate_up GEMM live in symmetric memory (the peers' dispatch kernels
+        write them); they are created first and handed to the parent's allocation under their names."""
         self.peer_q8 = self.peer_f16 = self.peer_sc = None
-        # decided from ALL experts' formats, not the local ones: the rendezvous is collective and senders quantize per expert
-        if any(a < 16 for a, _ in self.q_all):
-            self.x_q8, self.peer_q8, _ = shared((cap, H), torch.int8)
-            self.x_sc, self.peer_sc, _ = shared((cap, cols), torch.float16)
-        if any(a >= 16 for a, _ in self.q_all):
-            self.x_f16, self.peer_f16, _ = shared((cap, H), torch.float16)
-        self.back, self.peer_back, _ = shared((R, H), torch.float16)
-        self.counts_all, self.peer_counts, self.sync = shared((W, E), torch.int32)
-        self.back_row = torch.zeros(W * self.EL, dtype=torch.int32, device=d)
-        self.dest = torch.zeros(E * ctypes.sizeof(ops.MxbRowDest), dtype=torch.uint8, device=d)
+        if self.push:
+            cap, H, cols = self.cap_rows, self.H, self._scale_cols
+            ov = {"x_q8": None, "x_sc": None, "x_f16": None}
+            # decided from ALL experts' formats, not the local ones: the rendezvous is collective and senders quantize per expert
+            if any(a < 16 for a, _ in self.q_all):
+                ov["x_q8"], self.peer_q8, _ = self._symm("x_q8", (cap, H), torch.int8)
+                ov["x_sc"], self.peer_sc, _ = self._symm("x_sc", (cap, cols), torch.float16)
+            if any(a >= 16 for a, _ in self.q_all):
+                ov["x_f16"], self.peer_f16, _ = self._symm("x_f16", (cap, H), torch.float16)
+            self._override = ov
+        super()._alloc(T)
+        if self.push:  # local experts may use fewer formats than the senders: keep every receive buffer reachable
+            self.x_q8, self.x_sc, self.x_f16 = self._override["x_q8"], self._override["x_sc"], self._override["x_f16"]
+
+    def _setup_push(self, R: int, H: int, cols: int):
+        """Return buffer, count matrix and the device-side plan of the push exchange."""
+        W, E = self.W, self.E
+        fresh = ("symm", "counts_all", (W, E), torch.int32) not in self._pool
+        self.back, self.peer_back, _ = self._symm("back", (R, H), torch.float16)
+        self.counts_all, self.peer_counts, self.sync = self._symm("counts_all", (W, E), torch.int32)
+        self.back_row = self._buf("back_row", (W * self.EL,), torch.int32, zero=True)
+        self.dest = self._buf("dest", (E * ctypes.sizeof(ops.MxbRowDest),), torch.uint8, zero=True)
         self.scale_cols = cols
-        torch.cuda.synchronize()
-        dist.barrier(group=self.group)
+        if fresh:
+            torch.cuda.synchronize()
+            dist.barrier(group=self.group)
 
     def _build_segment_problems(self):
         H, I = self.H, self.I
@@ -395,6 +417,15 @@ class EPMoELayer(MoELayer):
         h.group_gemm(self._dn_arr)
 
     # ------------------------------------------------------------------ bench helpers
+    def gemm_only(self):
+        """Re-issue every GroupGEMM launch of the last step on its buffers: the routed segment lists AND, when the
+        replicated shared expert runs through its own lists (overlap), those too — the launches gemm_ops() counts."""
+        self.h.group_gemm(self._gu_arr)
+        self.h.group_gemm(self._dn_arr)
+        if getattr(self, "overlap", False):
+            self.h.group_gemm(self._sgu_arr)
+            self.h.group_gemm(self._sdn_arr)
+
     def last_counts(self):
         """rows per local expert processed in the last step (summed over sources)"""
         if self.push:

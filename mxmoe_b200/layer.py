@@ -51,13 +51,17 @@ class MoELayer:
     def __init__(self, handle: ops.Handle, E: int, topk: int, H: int, I: int, ns: int, qlayer: QLayerConfig,
                  max_tokens: int, hadamard_down: bool = False, expert_ids: Optional[Sequence[int]] = None, seed: int = 42,
                  weights: Optional[dict] = None, device: Optional[torch.device] = None, weight_scale: float = 1.0,
-                 fuse_silu: bool = True, packed: Optional[dict] = None):
+                 fuse_silu: bool = True, packed: Optional[dict] = None, share: Optional["MoELayer"] = None):
         """expert_ids: the routed experts this rank owns (expert-parallel shard); default all E.
-        weights: optional {expert_idx: (W_gate_up fp16 [2I',H], W_down fp16 [H,I'])}; default U(-1,1) seed 42
-        (the reference bench's distribution, test.cu:877-915).
+        weights: optional {expert_idx: (W_gate_up fp16 [2I',H], W_down fp16 [H,I'])}, may cover some experts only; the
+        others draw U(-1,1) * weight_scale from a generator seeded per expert (the reference bench's distribution,
+        test.cu:877-915).
         packed: a stored layer (checkpoint.load_packed(...)[layer]): operands already in their native layouts, copied as
-        they are — no fp16 weights and no quantization pass."""
+        they are — no fp16 weights and no quantization pass.
+        share: another layer of the same stack whose activation / routing buffers this layer re-uses (the layers of a stack
+        run one after the other on one stream, so one set of buffers serves all of them; weights stay per layer)."""
         self.h = handle
+        self._pool = share._pool if share is not None else {}
         self.E, self.topk, self.H, self.I, self.ns = E, topk, H, I, ns
         self.hadamard_down = hadamard_down
         self.dev = device or torch.device("cuda", handle.device)
@@ -81,7 +85,7 @@ class MoELayer:
         # every element of h is then computed once, not once per CTA that stages the row for the down projection.
         # fuse_silu=False or MXB_STREAM_EPI=0 keeps the staging form (MXB_PRO_SILU_MUL over stacked rows).
         self.stream_epi = self.stream_fused and fuse_silu and os.environ.get("MXB_STREAM_EPI", "1") != "0"
-        gen = torch.Generator(device=self.dev).manual_seed(seed)
+        gen = torch.Generator(device=self.dev)
         ids = self.local_experts + ([E] if ns else [])
         # Stored rows against this layer's row order.  Only the decode form depends on the batch size, so only there the loader
         # adapts: stacked rows keep the staging form; interleaved rows of a decode record are put back in [gate; up] order for a
@@ -120,6 +124,9 @@ class MoELayer:
                 Wgu, Wdn = weights[e]
                 Wgu, Wdn = Wgu.to(self.dev), Wdn.to(self.dev)
             else:
+                # one stream per expert: expert e has the same weights whichever rank owns it and however many experts the
+                # layer holds (an expert-parallel shard, the single-GPU layer it is checked against, the replicated shared expert)
+                gen.manual_seed(seed * 1000003 + e)
                 Wgu = torch.rand(2 * Ie, H, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).mul_(weight_scale).half()
                 Wdn = torch.rand(H, Ie, generator=gen, device=self.dev, dtype=torch.float32).mul_(2).sub_(1).mul_(weight_scale).half()
             gu_p, gu_s = self._pack(Wgu, qe.gate)
@@ -146,42 +153,56 @@ class MoELayer:
             return W.contiguous(), None
         return self.h.quant_pack_weight(W, q.w_bits, q.a_bits, q.w_gsize, q.w_sym)
 
+    def _buf(self, name: str, shape, dtype, zero: bool = False) -> torch.Tensor:
+        """A buffer of the stack's pool: layers built with `share=` get the tensor an earlier layer allocated under the same
+        (name, shape, dtype), so the problem lists of every layer of a stack point at one set of activation buffers."""
+        ov = getattr(self, "_override", None)
+        if ov is not None and name in ov:  # a subclass supplies this buffer (expert-parallel receive buffers in peer-mapped memory)
+            return ov[name]
+        key = (name, tuple(int(v) for v in shape), dtype)
+        t = self._pool.get(key)
+        if t is None:
+            t = (torch.zeros if zero else torch.empty)(*key[1], dtype=dtype, device=self.dev)
+            self._pool[key] = t
+        return t
+
     def _alloc(self, T: int):
-        d, H, I, k = self.dev, self.H, self.I, self.topk
+        H, I, k = self.H, self.I, self.topk
         R = T * k  # routed rows (capacity: every token could land on this rank)
         f16, i8 = torch.float16, torch.int8
+        B = self._buf
         qs = [e.q_gu for e in self.experts[:self.EL]] + [e.q_dn for e in self.experts[:self.EL]]
         any_q = any(q.a_bits < 16 for q in qs)
         any_f = any(q.a_bits >= 16 for q in qs)
         any_q_dn = any(e.q_dn.a_bits < 16 for e in self.experts[:self.EL])
         g_gu = any(q.a_bits < 16 and q.a_gsize == 128 for q in [e.q_gu for e in self.experts[:self.EL]])
         g_dn = any(q.a_bits < 16 and q.a_gsize == 128 for q in [e.q_dn for e in self.experts[:self.EL]])
-        self.x_q8 = torch.empty(R, H, dtype=i8, device=d) if any_q else None
-        self.x_f16 = torch.empty(R, H, dtype=f16, device=d) if any_f else None
-        self.x_sc = torch.empty(R, H // 128 if g_gu else 1, dtype=f16, device=d) if any_q else None
+        self.x_q8 = B("x_q8", (R, H), i8) if any_q else None
+        self.x_f16 = B("x_f16", (R, H), f16) if any_f else None
+        self.x_sc = B("x_sc", (R, H // 128 if g_gu else 1), f16) if any_q else None
         # gate_up output: [R, 2I] (two-step) or already silu(gate)*up [R, I] (fused epilogue)
-        self.gu_out = torch.empty(R, I if self.fused_silu else 2 * I, dtype=f16, device=d)
+        self.gu_out = B("gu_out", (R, I if self.fused_silu else 2 * I), f16)
         # fp16-only down experts without a rotation consume the fused output directly
         self.h_direct = self.fused_silu and not any_q_dn and not self.hadamard_down
-        self.h_q8 = torch.empty(R, I, dtype=i8, device=d) if any_q else None
-        self.h_f16 = (self.gu_out if self.h_direct else torch.empty(R, I, dtype=f16, device=d)) if any_f else None
-        self.h_sc = torch.empty(R, I // 128 if g_dn else 1, dtype=f16, device=d) if any_q else None
-        self.dn_out = torch.empty(R, H, dtype=f16, device=d)
+        self.h_q8 = B("h_q8", (R, I), i8) if any_q else None
+        self.h_f16 = (self.gu_out if self.h_direct else B("h_f16", (R, I), f16)) if any_f else None
+        self.h_sc = B("h_sc", (R, I // 128 if g_dn else 1), f16) if any_q else None
+        self.dn_out = B("dn_out", (R, H), f16)
         if self.ns:
             s = self.experts[-1]
             Is = I * self.ns
-            self.sx_q8 = torch.empty(T, H, dtype=i8, device=d) if s.q_gu.a_bits < 16 else None
-            self.sx_sc = torch.empty(T, H // 128 if s.q_gu.a_gsize == 128 else 1, dtype=f16, device=d) if s.q_gu.a_bits < 16 else None
-            self.s_gu = torch.empty(T, Is if self.fused_silu else 2 * Is, dtype=f16, device=d)
+            self.sx_q8 = B("sx_q8", (T, H), i8) if s.q_gu.a_bits < 16 else None
+            self.sx_sc = B("sx_sc", (T, H // 128 if s.q_gu.a_gsize == 128 else 1), f16) if s.q_gu.a_bits < 16 else None
+            self.s_gu = B("s_gu", (T, Is if self.fused_silu else 2 * Is), f16)
             self.sh_direct = self.fused_silu and s.q_dn.a_bits >= 16 and not self.hadamard_down
             # like the reference workload (gen_workload.py:101) the shared down problem takes the gate config
-            self.sh_q8 = torch.empty(T, Is, dtype=i8, device=d) if s.q_dn.a_bits < 16 else None
-            self.sh_f16 = (self.s_gu if self.sh_direct else torch.empty(T, Is, dtype=f16, device=d)) if s.q_dn.a_bits >= 16 else None
-            self.sh_sc = torch.empty(T, Is // 128 if s.q_dn.a_gsize == 128 else 1, dtype=f16, device=d) if s.q_dn.a_bits < 16 else None
-            self.s_dn = torch.empty(T, H, dtype=f16, device=d)
-        self.offs = torch.zeros(self.EL + 1, dtype=torch.int32, device=d)
-        self.src = torch.zeros(R, dtype=torch.int32, device=d)      # permute outputs live in fixed buffers: problem lists
-        self.slot = torch.zeros(T, k, dtype=torch.int32, device=d)  # (a_rows) and CUDA graphs keep their addresses
+            self.sh_q8 = B("sh_q8", (T, Is), i8) if s.q_dn.a_bits < 16 else None
+            self.sh_f16 = (self.s_gu if self.sh_direct else B("sh_f16", (T, Is), f16)) if s.q_dn.a_bits >= 16 else None
+            self.sh_sc = B("sh_sc", (T, Is // 128 if s.q_dn.a_gsize == 128 else 1), f16) if s.q_dn.a_bits < 16 else None
+            self.s_dn = B("s_dn", (T, H), f16)
+        self.offs = B("offs", (self.EL + 1,), torch.int32, zero=True)
+        self.src = B("src", (R,), torch.int32, zero=True)      # permute outputs live in fixed buffers: problem lists
+        self.slot = B("slot", (T, k), torch.int32, zero=True)  # (a_rows) and CUDA graphs keep their addresses
 
     def _problem(self, q: QLinearConfig, A_q8, A_f16, sc, B, sb, C, rows, N, K, m_range, flags=0, c_row=None, a_rows=None):
         A = A_f16 if q.a_bits >= 16 else A_q8
@@ -292,8 +313,7 @@ class MoELayer:
             h.group_gemm(self._gu_arr)
             h.group_gemm(self._dn_arr)
             return
-        if True:
-            h.quant_act(x, src_row, n_rows, self.offs, self.actq_gu(), False, self.x_q8, self.x_f16, self.x_sc)
+        h.quant_act(x, src_row, n_rows, self.offs, self.actq_gu(), False, self.x_q8, self.x_f16, self.x_sc)
         if self.ns:
             s = self.experts[-1]
             if s.q_gu.a_bits < 16:

@@ -23,8 +23,15 @@ from mxmoe_b200 import config as C  # noqa: E402
 from mxmoe_b200 import workload as W  # noqa: E402
 
 
-def build_problems(h, ops, torch, plist, seed=42):
-    """One Problem per workload entry with M > 0 (empty problems are skipped like ref_bind.cu:360)."""
+def qstr_of(p) -> str:
+    if p["w_bits"] == 16 and p["a_bits"] == 16:
+        return "fp16"
+    return f"w{p['w_bits']}a{p['a_bits']}_g{p['gsize']}_{'sym' if p['sym'] else 'asym'}"
+
+
+def build_problems(h, ops, torch, plist, seed=42, tile_n_of=None):
+    """One Problem per workload entry with M > 0 (empty problems are skipped like ref_bind.cu:360).
+    tile_n_of: optional qstr -> MxbProblem.tile_n (from --tile_config; 0 = the library's own choice)."""
     g = torch.Generator(device="cuda").manual_seed(seed)
     probs, keep, total_ops = [], [], 0
     for p in plist:
@@ -35,17 +42,18 @@ def build_problems(h, ops, torch, plist, seed=42):
         A = (torch.rand(M, K, generator=g, device="cuda") * 2 - 1).half()
         Wt = (torch.rand(N, K, generator=g, device="cuda") * 2 - 1).half()
         Cb = torch.empty(M, N, dtype=torch.float16, device="cuda")
+        tn = tile_n_of(qstr_of(p)) if tile_n_of else 0
         if w_bits == 16 and a_bits == 16:
-            probs.append(ops.Problem(A, Wt, Cb, M, N, K))
+            probs.append(ops.Problem(A, Wt, Cb, M, N, K, tile_n=tn))
             keep += [A, Wt, Cb]
         else:
             packed, sc = h.quant_pack_weight(Wt, w_bits, a_bits, gsize, sym)
             if a_bits < 16:
                 q8, _, sa = h.quant_act(A, None, M, None, [(a_bits, gsize)])
-                probs.append(ops.Problem(q8, packed, Cb, M, N, K, w_bits, a_bits, gsize, True, scale_a=sa, scale_b=sc))
+                probs.append(ops.Problem(q8, packed, Cb, M, N, K, w_bits, a_bits, gsize, True, scale_a=sa, scale_b=sc, tile_n=tn))
                 keep += [q8, sa]
             else:
-                probs.append(ops.Problem(A, packed, Cb, M, N, K, w_bits, 16, gsize, sym, scale_b=sc))
+                probs.append(ops.Problem(A, packed, Cb, M, N, K, w_bits, 16, gsize, sym, scale_b=sc, tile_n=tn))
                 keep += [A]
             keep += [packed, sc, Cb]
             del Wt
@@ -120,8 +128,15 @@ def main():
     os.makedirs(os.path.join(ROOT, "out", "bench"), exist_ok=True)
     for L in layers:
         print(f"Processing Layer {L}...")
+        # --tile_config: the entry of every qconfig decides the kernel path / UMMA N of its problems (config.tile_hint)
+        hints = {q: C.tile_hint(C.tile_for(tiles, q, L, qcfg_list)) for q in qcfg_list}
+        if tiles:
+            print("  tile_config -> tile_n per qconfig (0 = selector's choice):", hints)
         for part in ("gate_up", "down"):
-            probs, keep, total_ops = build_problems(h, ops, torch, wl[f"layer-{L}"][part])
+            probs, keep, total_ops = build_problems(h, ops, torch, wl[f"layer-{L}"][part], tile_n_of=lambda q: hints.get(q, 0))
+            choice = h.select_tiles(probs)
+            paths = sorted({(c.path, c.tile_m, c.tile_n) for c in choice})
+            print(f"  {part}: kernel path / tile per problem kind: {paths}")
             arr = h.pack_problems(probs)
             ms = time_ms(torch, lambda: h.group_gemm(arr))
             As = [(torch.rand(p.M, p.K, device="cuda") - 0.5).half() for p in probs]

@@ -100,3 +100,44 @@ def test_gate_up_scale_interleave_roundtrip():
             assert torch.equal(w[:, 2 * i], v[:, i]) and torch.equal(w[:, 2 * i + 1], v[:, N // 2 + i])
         assert torch.equal(il(o, N, asym, inverse=True), s)
     assert il(None, N, False) is None
+
+
+def test_tile_config_entries_map_to_problem_hints(tmp_path):
+    """--tile_config is honoured (config.tile_for / tile_hint): both reference schemas and this library's own export."""
+    import json
+    from mxmoe_b200 import config as C
+    qcfgs = ["w4a4_g-1_sym", "w8a8_g-1_sym"]
+    # schema of compose_kernel.get_tile_configs (compose_kernel.py:87-91): {qcfg: [tiles]}, reference (sm_89) tile reprs
+    ref_repr = ("TileConfig(BM=128, BN=128, BK=128, WM=2, WN=2, WK=1, STAGE=3, SPLITK=-1, MMA='MMA_S4_K64', "
+                "QCFGA=QConfig(QBITS=4, GSIZE=-1, SYM=True), QCFGB=QConfig(QBITS=4, GSIZE=-1, SYM=True))")
+    p = tmp_path / "t.json"
+    json.dump({"w4a4_g-1_sym": [ref_repr], "w8a8_g-1_sym": [{"BM": 64, "BN": 96, "BK": 64}]}, open(p, "w"))
+    t = C.load_tile_config(str(p))
+    assert C.tile_hint(C.tile_for(t, "w4a4_g-1_sym", 11, qcfgs)) == 128   # reference tile: BN -> UMMA N of the single-CTA kernel
+    assert C.tile_hint(C.tile_for(t, "w8a8_g-1_sym", 11, qcfgs)) == 64    # rounded down to 32/64/128/256
+    assert C.tile_for(t, "fp16", 11, qcfgs) is None and C.tile_hint(None) == 0
+    # schema of bits_solver.export_qconfig (bits_solver.py:30,67-68): {layer: repr(tuple)}; the reference's is positional in
+    # the sorted strategy list, this library's carries QCFG / PATH
+    json.dump({"11": "(" + ref_repr + ", " + ref_repr.replace("BN=128", "BN=256") + ")",
+               "12": "(TileConfig(BM=256, BN=192, BK=128, WM=1, WN=1, WK=1, STAGE=6, SPLITK=-1, MMA='UMMA_I8_2CTA', PATH=2, "
+                     "QCFG='w8a8_g-1_sym'), TileConfig(BM=128, BN=64, BK=128, WM=1, WN=1, WK=1, STAGE=3, SPLITK=-1, MMA='UMMA_I8', "
+                     "PATH=0, QCFG='w4a4_g128_sym'))"}, open(p, "w"))
+    t = C.load_tile_config(str(p))
+    assert C.tile_hint(C.tile_for(t, "w4a4_g-1_sym", 11, qcfgs)) == 128
+    assert C.tile_hint(C.tile_for(t, "w8a8_g-1_sym", 11, qcfgs)) == 256
+    assert C.tile_hint(C.tile_for(t, "w8a8_g-1_sym", 12, qcfgs)) == 0     # PATH 2: the CTA-pair kernel picks its token tile
+    assert C.tile_hint(C.tile_for(t, "w4a4_g128_sym", 12, qcfgs)) == 64
+    assert C.tile_for(t, "w4a4_g-1_sym", 12, qcfgs) is None
+
+
+def test_solver_exports_tile_cfg_next_to_qconfig(tmp_path):
+    """bits_solver writes `<out>_tile_cfg.json` like the reference's export_qconfig (bits_solver.py:67-68), from mxb_select_tiles."""
+    import json
+    from mxmoe_b200 import bits_solver as B
+    from mxmoe_b200 import config as C
+    out = tmp_path / "q.json"
+    B.main(["--model", "qwen2_moe", "--wbits", "5.0", "--layers", "3", "--out", str(out)])
+    t = C.load_tile_config(str(tmp_path / "q_tile_cfg.json"))
+    assert set(t) == {"3"} and {e["QCFG"] for e in t["3"]} == {"w4a4_g-1_sym", "w8a8_g-1_sym"}
+    for e in t["3"]:
+        assert e["PATH"] == 2 and e["BM"] == 256 and e["BN"] % 16 == 0 and e["MMA"] == "UMMA_I8_2CTA"
