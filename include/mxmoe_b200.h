@@ -155,12 +155,28 @@ int mxb_group_gemm_debug_acc(mxb_handle_t h, const MxbProblem* problems, int pro
                              int32_t* const* acc_out, void* stream);
 /* Verbatim FuncType argument list (registry.cuh:28-39): device SoA arrays plus host copies of sizes/QParams.
  * sizes are 3x uint32 (dim3: M,N,K); qparams are {int a_bits; int w_bits; int gsize; bool sym} = 16 bytes
- * (quantize.cuh:14-25).  Operands must be in the native layouts above.  Uses the handle's own stream 0
- * semantics like the reference when stream == NULL. */
+ * (quantize.cuh:14-25).  Problems with M = 0 are skipped like the reference's callers do (ref_bind.cu:360).  Operand
+ * layouts: the native ones above, or — after mxb_set_ref_operands(h, MXB_REF_OPERANDS) — the REFERENCE's packed layouts
+ * exactly as its callers hold them (A and B of WxAx problems from pack_wxax, B of weight-only problems from
+ * permute_weight + pack_weightonly, scales in the permute_scale layout): the shim converts A on every call and B once
+ * per weight pointer into handle-owned buffers, so a test.cu-style caller (test.cu:794-814) links unchanged.
+ * stream == NULL is the default stream, as in the reference (kernel_sketch.py:123). */
 int mxb_group_gemm_reflayout(mxb_handle_t h, void** ptr_As, void** ptr_Bs, void** ptr_scale_a, void** ptr_scale_b,
                              void** ptr_Cs, void** ptr_Ds, int64_t* ldas, int64_t* ldbs, int64_t* ldcs,
                              int64_t* ldds, const void* dev_problem_sizes, const void* host_problem_sizes,
                              const void* dev_qparams, const void* host_qparams, int problem_count, void* stream);
+
+/* How mxb_group_gemm_reflayout reads its operands (bit mask, default 0):
+ *   MXB_REF_OPERANDS      A / B are in the reference's packed layouts (see above); converted inside the call.
+ *   MXB_REF_TABLES_FIXED  the five device pointer tables do not change between calls with the same table addresses and
+ *                         problem count: they are fetched once instead of on every call (5 blocking D2H copies + a stream
+ *                         synchronisation per call otherwise, which is what the reference's own launcher costs too). */
+#define MXB_REF_OPERANDS 1
+#define MXB_REF_TABLES_FIXED 2
+int mxb_set_ref_operands(mxb_handle_t h, int flags);
+/* The A half of pack_wxax (quantize.cuh:424-475; uint16 words along K, first element in the most significant bits)
+ * -> int8 containers [M, K] as mxb_quant_act writes them.  a_bits 8 or 4. */
+int mxb_repack_act_from_ref(mxb_handle_t h, const void* ref_packed, int64_t M, int K, int a_bits, void* out_q8, void* stream);
 
 /* ---- piece (1): token -> expert permute ---- */
 /* topk_ids int32 [T,k] with values in [0,E).  Outputs: expert_offsets int32 [E+1]; src_row int32 [T*k]

@@ -86,6 +86,14 @@ struct mxb_context {
   std::vector<std::pair<int, void*>> hads;            // device fp16 copies of the K x K Hadamard factors
   cudaStream_t aux = nullptr;                         // fork/join side stream: tcgen05 kernel next to the streaming kernel
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // mxb_group_gemm_reflayout in reference-operand mode (mxb_set_ref_operands)
+  int ref_flags = 0;
+  struct RefWeight { const void* src; int N, K, w_bits, a_bits; void* native; };
+  std::vector<RefWeight> ref_weights;                 // reference-packed B -> native copy, converted once per pointer
+  void* ref_act = nullptr;                            // scratch for the converted A operands of one call
+  size_t ref_act_bytes = 0;
+  struct RefTables { const void* key[5]; int P; std::vector<void*> host[5]; };
+  std::vector<RefTables> ref_tables;                  // fetched pointer tables (MXB_REF_TABLES_FIXED)
 };
 
 namespace {
@@ -479,6 +487,8 @@ int mxb_destroy(mxb_handle_t c) {
   for (auto* p : c->inv_tab)
     if (p) cudaFree(p);
   for (auto& h : c->hads) cudaFree(h.second);
+  for (auto& w : c->ref_weights) cudaFree(w.native);
+  if (c->ref_act) cudaFree(c->ref_act);
   if (c->ws) cudaFree(c->ws);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
@@ -524,6 +534,23 @@ int mxb_group_gemm_debug_acc(mxb_handle_t c, const MxbProblem* problems, int pro
   return group_gemm_impl(c, problems, problem_count, acc_out, stream);
 }
 
+int mxb_set_ref_operands(mxb_handle_t c, int flags) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (flags & ~(MXB_REF_OPERANDS | MXB_REF_TABLES_FIXED)) return fail(MXB_EINVAL, "unknown flags 0x%x", flags);
+  c->ref_flags = flags;
+  return MXB_OK;
+}
+
+int mxb_repack_act_from_ref(mxb_handle_t c, const void* ref_packed, int64_t M, int K, int a_bits, void* out_q8, void* stream) {
+  if (!c) return fail(MXB_EINVAL, "null handle");
+  if (!(a_bits == 8 || a_bits == 4)) return fail(MXB_EINVAL, "a_bits %d: pack_wxax holds 8- or 4-bit values", a_bits);
+  if (M < 0 || K <= 0 || K % (16 / a_bits) != 0) return fail(MXB_EINVAL, "bad shape %lld x %d", (long long)M, K);
+  if (M > 0 && (!ref_packed || !out_q8)) return fail(MXB_EINVAL, "null pointer");
+  CU_OK(cudaSetDevice(c->device));
+  CU_OK(mxb::repack_act_launch(ref_packed, M, K, a_bits, out_q8, static_cast<cudaStream_t>(stream)));
+  return MXB_OK;
+}
+
 int mxb_group_gemm_reflayout(mxb_handle_t c, void** ptr_As, void** ptr_Bs, void** ptr_scale_a, void** ptr_scale_b,
                              void** ptr_Cs, void** ptr_Ds, int64_t* ldas, int64_t* ldbs, int64_t* ldcs, int64_t* ldds,
                              const void* dev_problem_sizes, const void* host_problem_sizes, const void* dev_qparams,
@@ -532,20 +559,52 @@ int mxb_group_gemm_reflayout(mxb_handle_t c, void** ptr_As, void** ptr_Bs, void*
   if (!c) return fail(MXB_EINVAL, "null handle");
   if (P <= 0) return P == 0 ? MXB_OK : fail(MXB_EINVAL, "negative problem count");
   if (!host_problem_sizes || !host_qparams) return fail(MXB_EINVAL, "host copies of sizes/qparams are required");
+  if (!ptr_As || !ptr_Bs || !ptr_Cs) return fail(MXB_EINVAL, "null pointer table");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  std::vector<void*> hA(P), hB(P), hSa(P), hSb(P), hC(P);
-  // the pointer tables live on the device in the reference's contract: fetch them (synchronous, like the
-  // reference launcher's own cudaMemcpy)
-  CU_OK(cudaMemcpyAsync(hA.data(), ptr_As, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
-  CU_OK(cudaMemcpyAsync(hB.data(), ptr_Bs, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
-  CU_OK(cudaMemcpyAsync(hC.data(), ptr_Cs, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
-  if (ptr_scale_a) CU_OK(cudaMemcpyAsync(hSa.data(), ptr_scale_a, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
-  if (ptr_scale_b) CU_OK(cudaMemcpyAsync(hSb.data(), ptr_scale_b, sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
-  CU_OK(cudaStreamSynchronize(st));
+  CU_OK(cudaSetDevice(c->device));
+  // The pointer tables live on the device in the reference's contract.  Default: fetch them on every call (synchronous,
+  // like the reference launcher's own cudaMemcpy); MXB_REF_TABLES_FIXED: once per (table addresses, P).
+  const void* key[5] = {ptr_As, ptr_Bs, ptr_Cs, ptr_scale_a, ptr_scale_b};
+  mxb_context::RefTables* tab = nullptr;
+  if (c->ref_flags & MXB_REF_TABLES_FIXED)
+    for (auto& t : c->ref_tables)
+      if (t.P == P && memcmp(t.key, key, sizeof key) == 0) tab = &t;
+  mxb_context::RefTables local;
+  if (!tab) {
+    mxb_context::RefTables* dst = &local;
+    if (c->ref_flags & MXB_REF_TABLES_FIXED) {
+      if (c->ref_tables.size() >= 64) c->ref_tables.clear();
+      c->ref_tables.emplace_back();
+      dst = &c->ref_tables.back();
+    }
+    memcpy(dst->key, key, sizeof key);
+    dst->P = P;
+    for (int i = 0; i < 5; ++i) {
+      dst->host[i].assign(size_t(P), nullptr);
+      if (key[i]) CU_OK(cudaMemcpyAsync(dst->host[i].data(), key[i], sizeof(void*) * P, cudaMemcpyDeviceToHost, st));
+    }
+    CU_OK(cudaStreamSynchronize(st));
+    tab = dst;
+  }
+  const std::vector<void*>&hA = tab->host[0], &hB = tab->host[1], &hC = tab->host[2], &hSa = tab->host[3], &hSb = tab->host[4];
   struct Dim3 { uint32_t x, y, z; };
   struct QP { int32_t a_bits, w_bits, gsize; uint8_t sym; uint8_t pad[3]; };
   const Dim3* sz = static_cast<const Dim3*>(host_problem_sizes);
   const QP* qp = static_cast<const QP*>(host_qparams);
+  const bool ref_ops = (c->ref_flags & MXB_REF_OPERANDS) != 0;
+  size_t act_need = 0;
+  if (ref_ops)
+    for (int i = 0; i < P; ++i)
+      if (sz[i].x && qp[i].a_bits < 16) act_need += (size_t(sz[i].x) * sz[i].z + 255) & ~size_t(255);
+  if (act_need > c->ref_act_bytes) {
+    CU_OK(cudaStreamSynchronize(st));  // earlier launches may still read the old scratch
+    if (c->ref_act) cudaFree(c->ref_act);
+    c->ref_act = nullptr;
+    c->ref_act_bytes = 0;
+    CU_OK(cudaMalloc(&c->ref_act, act_need));
+    c->ref_act_bytes = act_need;
+  }
+  size_t act_off = 0;
   std::vector<MxbProblem> pr;
   pr.reserve(P);
   for (int i = 0; i < P; ++i) {
@@ -558,6 +617,28 @@ int mxb_group_gemm_reflayout(mxb_handle_t c, void** ptr_As, void** ptr_Bs, void*
     p.M = (int)sz[i].x; p.N = (int)sz[i].y; p.K = (int)sz[i].z;
     p.a_bits = qp[i].a_bits; p.w_bits = qp[i].w_bits; p.gsize = qp[i].gsize; p.sym = qp[i].sym ? 1 : 0;
     if (p.a_bits == 16 && p.w_bits == 16) { p.gsize = -1; p.sym = 1; }
+    if (ref_ops && !(p.a_bits == 16 && p.w_bits == 16)) {
+      if (p.a_bits < 16) {  // A: the caller's packed halves -> int8 containers, every call (activations change)
+        void* dstA = static_cast<char*>(c->ref_act) + act_off;
+        act_off += (size_t(p.M) * p.K + 255) & ~size_t(255);
+        int rc = mxb_repack_act_from_ref(c, p.A, p.M, p.K, p.a_bits, dstA, stream);
+        if (rc) return rc;
+        p.A = dstA;
+      }
+      void* nat = nullptr;  // B: converted once per weight pointer
+      for (auto& w : c->ref_weights)
+        if (w.src == p.B && w.N == p.N && w.K == p.K && w.w_bits == p.w_bits && w.a_bits == p.a_bits) nat = w.native;
+      if (!nat) {
+        CU_OK(cudaMalloc(&nat, size_t(mxb_packed_bytes(p.N, p.K, p.w_bits))));
+        int rc = mxb_repack_from_ref(c, p.B, p.N, p.K, p.w_bits, p.a_bits, p.sym, nat, stream);
+        if (rc) {
+          cudaFree(nat);
+          return rc;
+        }
+        c->ref_weights.push_back({p.B, p.N, p.K, p.w_bits, p.a_bits, nat});
+      }
+      p.B = nat;
+    }
     pr.push_back(p);
   }
   return group_gemm_impl(c, pr.data(), (int)pr.size(), nullptr, stream);

@@ -514,6 +514,27 @@ __global__ void __launch_bounds__(256) repack_wxax_kernel(const uint16_t* __rest
   }
 }
 
+// Reference WxAx ACTIVATION layout (the A half of pack_wxax, quantize.cuh:424-475: uint16 words along K, first element in
+// the most significant bits, two's complement) -> int8 containers [M, K] (4-bit values sign-extended).
+__global__ void __launch_bounds__(256) repack_act_kernel(const uint16_t* __restrict__ ref, int64_t n_words, int bits,
+                                                          int8_t* __restrict__ out) {
+  const int pack = 16 / bits;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x; i < n_words; i += static_cast<int64_t>(gridDim.x) * 256) {
+    const uint16_t wv = ref[i];
+    if (bits == 8) {
+      *reinterpret_cast<uint16_t*>(out + i * 2) = static_cast<uint16_t>((wv >> 8) | (wv << 8));
+    } else {
+      uint32_t o = 0;
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {
+        const int v = (wv >> (4 * (3 - x))) & 0xF;
+        o |= static_cast<uint32_t>(static_cast<uint8_t>(static_cast<int8_t>((v ^ 8) - 8))) << (8 * x);
+      }
+      *reinterpret_cast<uint32_t*>(out + i * pack) = o;
+    }
+  }
+}
+
 // Reference W-only layout (permute_weight + pack_weightonly, quantize.cuh:318-421) -> native layouts 2 / 3.
 // `inv` maps (row in a PACK*8-row block, k in a 16-k block) -> flat index of the value inside the
 // permuted block as it was before packing; built on the host from the reference's permutation tables.
@@ -559,6 +580,15 @@ cudaError_t quant_pack_weight_launch(const void* W, int N, int K, int bits, int 
 
 cudaError_t repack_wxax_launch(const void* ref, int N, int K, int bits, void* packed, cudaStream_t st) {
   repack_wxax_kernel<<<N, 256, K, st>>>(static_cast<const uint16_t*>(ref), N, K, bits, static_cast<uint8_t*>(packed));
+  return cudaGetLastError();
+}
+
+cudaError_t repack_act_launch(const void* ref, int64_t M, int K, int bits, void* out, cudaStream_t st) {
+  const int64_t n_words = M * K * bits / 16;
+  if (n_words == 0) return cudaSuccess;
+  int64_t grid = (n_words + 255) / 256;
+  if (grid > 148 * 16) grid = 148 * 16;
+  repack_act_kernel<<<static_cast<unsigned>(grid), 256, 0, st>>>(static_cast<const uint16_t*>(ref), n_words, bits, static_cast<int8_t*>(out));
   return cudaGetLastError();
 }
 

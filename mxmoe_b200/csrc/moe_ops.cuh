@@ -38,6 +38,7 @@ cudaError_t combine_launch(const void* down, int H, const int32_t* slot_of, cons
 cudaError_t quant_pack_weight_launch(const void* W, int N, int K, int bits, int gsize, int sym, int layout, void* packed,
                                      void* scales, cudaStream_t st);
 cudaError_t repack_wxax_launch(const void* ref, int N, int K, int bits, void* packed, cudaStream_t st);
+cudaError_t repack_act_launch(const void* ref, int64_t M, int K, int bits, void* out, cudaStream_t st);
 cudaError_t repack_wonly_launch(const void* ref, int N, int K, int bits, const int32_t* inv_dev, void* packed,
                                 cudaStream_t st);
 

@@ -378,6 +378,37 @@ class MoELayer:
         return tot
 
 
+class MoEStack:
+    """The MoE blocks of a model's decoder stack, one after the other on one stream (BASELINE configs[4]: "full MoE stack"):
+    per-layer weights and qconfigs (the solver assigns bit-widths layer by layer, ref bits_solver.py:201-422), ONE set of
+    activation / routing / exchange buffers (`share=`).  In a decoder the attention block and the norms sit between two MoE
+    blocks, so every block's input is a fresh normalised hidden state: forward() feeds the same batch `x` to every block
+    with that block's own routing (topk_ids[l], topk_w[l]); `out` holds the last block's result when it returns."""
+
+    def __init__(self, layers: Sequence["MoELayer"]):
+        assert len(layers) >= 1
+        self.layers = list(layers)
+        l0 = self.layers[0]
+        self.dev, self.H, self.topk, self.E = l0.dev, l0.H, l0.topk, l0.E
+
+    def forward(self, x: torch.Tensor, topk_ids: torch.Tensor, topk_w: torch.Tensor, out: Optional[torch.Tensor] = None, marks=None):
+        """topk_ids int32 [L, T, k], topk_w fp32 [L, T, k].  marks: optional list that receives one CUDA event per block end."""
+        for i, layer in enumerate(self.layers):
+            out = layer.forward(x, topk_ids[i], topk_w[i], out)
+            if marks is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                marks.append(ev)
+        return out
+
+    def gemm_only(self):
+        for layer in self.layers:
+            layer.gemm_only()
+
+    def launches_per_step(self) -> int:
+        return sum(layer.launches_per_step() for layer in self.layers)
+
+
 class HostPipeline:
     """Streams HOST-resident batches through a layer: the call a user with pinned host buffers makes.
 
@@ -393,10 +424,13 @@ class HostPipeline:
         self.graph = graph
         self.s_in, self.s_out = torch.cuda.Stream(d), torch.cuda.Stream(d)
         self.slots = []
+        stack = isinstance(layer, MoEStack)
+        rshape = (len(layer.layers), T, layer.topk) if stack else (T, layer.topk)  # a stack takes every block's routing
+        self.tdim = 1 if stack else 0
         for _ in range(depth):
             self.slots.append(dict(
-                x=torch.empty(T, layer.H, dtype=torch.float16, device=d), ids=torch.empty(T, layer.topk, dtype=torch.int32, device=d),
-                w=torch.empty(T, layer.topk, dtype=torch.float32, device=d), out=torch.empty(T, layer.H, dtype=torch.float16, device=d),
+                x=torch.empty(T, layer.H, dtype=torch.float16, device=d), ids=torch.empty(rshape, dtype=torch.int32, device=d),
+                w=torch.empty(rshape, dtype=torch.float32, device=d), out=torch.empty(T, layer.H, dtype=torch.float16, device=d),
                 up=torch.cuda.Event(), done=torch.cuda.Event(), down=torch.cuda.Event(), g=None, T=None))
         self.n = 0
 
@@ -406,19 +440,20 @@ class HostPipeline:
         cur = torch.cuda.current_stream()
         T = x_host.shape[0]
         self.s_in.wait_event(sl["done"])  # the kernels that last read this slot's inputs are finished
+        ids_d, w_d = sl["ids"].narrow(self.tdim, 0, T), sl["w"].narrow(self.tdim, 0, T)
         with torch.cuda.stream(self.s_in):
             sl["x"][:T].copy_(x_host, non_blocking=True)
-            sl["ids"][:T].copy_(ids_host, non_blocking=True)
-            sl["w"][:T].copy_(w_host, non_blocking=True)
+            ids_d.copy_(ids_host, non_blocking=True)
+            w_d.copy_(w_host, non_blocking=True)
             sl["up"].record(self.s_in)
         cur.wait_event(sl["up"])
         cur.wait_event(sl["down"])        # the previous download of this slot's output is finished
         if self.graph:
             if sl["g"] is None or sl["T"] != T:
-                sl["g"], sl["T"] = self.layer.capture(sl["x"][:T], sl["ids"][:T], sl["w"][:T], sl["out"][:T]), T
+                sl["g"], sl["T"] = self.layer.capture(sl["x"][:T], ids_d, w_d, sl["out"][:T]), T
             sl["g"].replay()
         else:
-            self.layer.forward(sl["x"][:T], sl["ids"][:T], sl["w"][:T], sl["out"][:T])
+            self.layer.forward(sl["x"][:T], ids_d, w_d, sl["out"][:T])
         sl["done"].record(cur)
         self.s_out.wait_event(sl["done"])
         with torch.cuda.stream(self.s_out):

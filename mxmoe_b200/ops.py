@@ -71,6 +71,8 @@ EXPORTS = [
     ("mxb_group_gemm", _I, [_P, C.POINTER(MxbProblem), _I, _P]),
     ("mxb_group_gemm_debug_acc", _I, [_P, C.POINTER(MxbProblem), _I, C.POINTER(_P), _P]),
     ("mxb_group_gemm_reflayout", _I, [_P] + [_P] * 14 + [_I, _P]),
+    ("mxb_set_ref_operands", _I, [_P, _I]),
+    ("mxb_repack_act_from_ref", _I, [_P, _P, _I64, _I, _I, _P, _P]),
     ("mxb_permute", _I, [_P, _P, _I, _I, _I, _P, _P, _P, _P]),
     ("mxb_quant_act", _I, [_P, _P, _I, _P, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),
     ("mxb_silu_mul_quant", _I, [_P, _P, _I, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),

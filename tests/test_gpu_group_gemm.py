@@ -495,3 +495,116 @@ def test_e4m3_mixed_list_and_device_quantizers(H):
     pf, reff, _ = make_problem(ops, rng, 64, 128, 256, 16, 16, -1, True)
     H.group_gemm([p8, pi, pf])
     check([p8, pi, pf], [O.gemm_e4m3(va, sa, vw, sw), refi, reff], [None, None, None])
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# The FuncType shim (mxb_group_gemm_reflayout), driven exactly as INTEGRATION.md section 1's adaptor drives it:
+# device `half**` tables, device + host dim3 arrays, device + host 16-byte QParams (registry.cuh:28-39,
+# quantize.cuh:14-25, caller test.cu:794-814), NULL stream.
+import ctypes as _C
+
+
+class _Dim3(_C.Structure):
+    _fields_ = [("x", _C.c_uint32), ("y", _C.c_uint32), ("z", _C.c_uint32)]
+
+
+class _QParams(_C.Structure):  # {int2 qbits (x = a_bits, y = w_bits); int gsize; bool sym}
+    _fields_ = [("a_bits", _C.c_int32), ("w_bits", _C.c_int32), ("gsize", _C.c_int32), ("sym", _C.c_uint8), ("pad", _C.c_uint8 * 3)]
+
+
+def _call_shim(h, A, B, sa, sb, Cs, shapes, quants):
+    P = len(shapes)
+    tab = lambda ts: torch.tensor([t.data_ptr() if t is not None else 0 for t in ts], dtype=torch.int64, device="cuda")
+    tA, tB, tsa, tsb, tC = tab(A), tab(B), tab(sa), tab(sb), tab(Cs)
+    hs = (_Dim3 * P)(*[_Dim3(*s) for s in shapes])
+    hq = (_QParams * P)(*[_QParams(a, w, g, 1 if sym else 0) for (w, a, g, sym) in quants])
+    ds = torch.frombuffer(bytearray(bytes(hs)), dtype=torch.uint8).cuda()
+    dq = torch.frombuffer(bytearray(bytes(hq)), dtype=torch.uint8).cuda()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(torch.cuda.default_stream()):
+        rc = h.lib.mxb_group_gemm_reflayout(h.h, tA.data_ptr(), tB.data_ptr(), tsa.data_ptr(), tsb.data_ptr(), tC.data_ptr(), tC.data_ptr(),
+                                            None, None, None, None, ds.data_ptr(), _C.addressof(hs), dq.data_ptr(), _C.addressof(hq), P, None)
+    torch.cuda.synchronize()
+    return rc
+
+
+_SHIM_LIST = [  # (M, N, K, w_bits, a_bits, gsize, sym): fp16, w8a8, an EMPTY problem, w4a4, w4a16 group-wise asym, w8a8 again
+    (200, 256, 256, 16, 16, -1, True), (300, 384, 512, 8, 8, -1, True), (0, 256, 512, 4, 4, -1, True),
+    (130, 256, 512, 4, 4, -1, True), (77, 256, 256, 4, 16, 128, False), (546, 128, 1024, 8, 8, -1, True)]
+
+
+@pytest.mark.parametrize("ref_operands", [False, True])
+def test_functype_shim_mixed_list(ref_operands):
+    """ref_operands=False: operands in the native layouts.  True: A and B exactly as a caller of the reference holds them
+    (pack_wxax halves, permute_weight + pack_weightonly words; quantize.cuh:318-475) after mxb_set_ref_operands — the shim
+    converts A per call and B once per weight pointer (second call: same result from the cached weights)."""
+    from mxmoe_b200 import ops
+    h = ops.Handle(0)
+    rng = np.random.default_rng(31)
+    A, B, sa, sb, Cs, shapes, quants, refs = [], [], [], [], [], [], [], []
+    for (M, N, K, wb, ab, g, sym) in _SHIM_LIST:
+        X, W = rand16(rng, max(M, 1), K)[:M], rand16(rng, N, K)
+        shapes.append((M, N, K))
+        quants.append((wb, ab, g, sym))
+        Cs.append(torch.full((max(M, 1), N), float("nan"), dtype=torch.float16, device="cuda"))
+        if wb == 16:
+            A.append(dev(X)); B.append(dev(W)); sa.append(None); sb.append(None)
+            refs.append(O.gemm_fp16(X, W))
+        elif ab == 16:
+            q, s, z = O.quant_weight(W, wb, g, sym)
+            A.append(dev(X))
+            B.append(dev(O.pack_weightonly_ref(q, wb, sym).view(np.int16)) if ref_operands else dev(O.pack_weightonly_native(q, wb, sym)))
+            sa.append(None); sb.append(dev(O.permute_scale(s, None if sym else z, sym)))
+            refs.append(O.gemm_wonly(X, q, s, z, g, sym))
+        else:
+            if M == 0:
+                qa, s_a = np.zeros((0, K), np.int32), np.zeros((0, 1), np.float16)
+            else:
+                qa, s_a = O.quant_act(X, ab, g)
+            qw, s_w, _ = O.quant_weight(W, wb, g, True)
+            if ref_operands:
+                A.append(dev(O.pack_wxax(qa, ab).view(np.int16)) if M else torch.zeros(1, dtype=torch.int16, device="cuda"))
+                B.append(dev(O.pack_wxax(qw, wb).view(np.int16)))
+            else:
+                A.append(dev(qa.astype(np.int8)) if M else torch.zeros(1, dtype=torch.int8, device="cuda"))
+                B.append(dev(O.pack_wxax_native(qw, wb)))
+            sa.append(dev(s_a.reshape(-1)) if M else torch.zeros(1, dtype=torch.float16, device="cuda"))
+            sb.append(dev(np.ascontiguousarray(s_w.T).reshape(-1)))
+            refs.append(O.gemm_wxax(qa, s_a, qw, s_w, g)[1] if M else None)
+    h._check(h.lib.mxb_set_ref_operands(h.h, (1 if ref_operands else 0)), "mxb_set_ref_operands")
+    for call in range(2):
+        for c in Cs:
+            c.fill_(float("nan"))
+        assert _call_shim(h, A, B, sa, sb, Cs, shapes, quants) == 0, h.lib.mxb_last_error().decode()
+        for (M, N, K, wb, ab, g, sym), c, r in zip(_SHIM_LIST, Cs, refs):
+            if M == 0:
+                continue
+            got = c.cpu().numpy()
+            if wb == 16 or ab == 16:
+                assert relerr(got, r) <= REL_TOL
+            else:
+                assert np.array_equal(got.view(np.uint16), r.view(np.uint16)), f"w{wb}a{ab} call {call}"
+
+
+def test_functype_shim_fixed_tables_and_errors():
+    """MXB_REF_TABLES_FIXED: the pointer tables are fetched once per (table addresses, P).  Unsupported QParams are an error
+    code, not an exception (the reference throws std::runtime_error, compose_kernel.py:433)."""
+    from mxmoe_b200 import ops
+    h = ops.Handle(0)
+    rng = np.random.default_rng(32)
+    M, N, K = 150, 256, 512
+    X, W = rand16(rng, M, K), rand16(rng, N, K)
+    qa, s_a = O.quant_act(X, 8, -1)
+    qw, s_w, _ = O.quant_weight(W, 8, -1, True)
+    ref = O.gemm_wxax(qa, s_a, qw, s_w, -1)[1]
+    A, B = [dev(qa.astype(np.int8))], [dev(O.pack_wxax_native(qw, 8))]
+    sa, sb = [dev(s_a.reshape(-1))], [dev(np.ascontiguousarray(s_w.T).reshape(-1))]
+    Cs = [torch.zeros(M, N, dtype=torch.float16, device="cuda")]
+    h._check(h.lib.mxb_set_ref_operands(h.h, 2), "mxb_set_ref_operands")
+    for _ in range(3):
+        Cs[0].zero_()
+        assert _call_shim(h, A, B, sa, sb, Cs, [(M, N, K)], [(8, 8, -1, True)]) == 0
+        assert np.array_equal(Cs[0].cpu().numpy().view(np.uint16), ref.view(np.uint16))
+    assert _call_shim(h, A, B, sa, sb, Cs, [(M, N, K)], [(3, 8, -1, True)]) == -1  # MXB_EINVAL
+    assert b"not supported" in h.lib.mxb_last_error()
+    assert h.lib.mxb_set_ref_operands(h.h, 8) == -1
