@@ -355,6 +355,7 @@ __global__ void __launch_bounds__(512, 2) hadamard_wide_kernel(HadParams p) {
 
 #include "hadamard_mma.inc"
 #include "hadamard_umma.inc"
+#include "hadamard_pipe.inc"
 
 }  // namespace
 
@@ -396,6 +397,20 @@ cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t
   p.h_pitch = Kp * 2 + 16;
   { const char* e = getenv("MXB_HAD_DBG"); p.dbg = e ? atoi(e) : 0; }
   static const int use_umma = [] { const char* e = getenv("MXB_HAD_UMMA"); return e ? atoi(e) : 1; }();
+  // warp-specialised tcgen05 pipeline (hadamard_pipe.inc); MXB_HAD_PIPE=0 keeps the phase-by-phase kernel below (tests
+  // compare the two bit for bit)
+  const char* pipe_env = getenv("MXB_HAD_PIPE");
+  const int use_pipe = pipe_env ? atoi(pipe_env) : 1;
+  if (use_pipe && use_umma && !silu && K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {
+    if (Kp == 176) return launch_pipe<11>(p, sm_count, st);
+    if (Kp == 160) return launch_pipe<10>(p, sm_count, st);
+    if (Kp == 144) return launch_pipe<9>(p, sm_count, st);
+    if (Kp == 112) return launch_pipe<7>(p, sm_count, st);
+    if (Kp == 64) return launch_pipe<4>(p, sm_count, st);
+    if (Kp == 48) return launch_pipe<3>(p, sm_count, st);
+    if (Kp == 32) return launch_pipe<2>(p, sm_count, st);
+    if (Kp == 16) return launch_pipe<1>(p, sm_count, st);
+  }
   if (use_umma && K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {  // tcgen05 form (hadamard_umma.inc)
     if (Kp == 176) return launch_umma<11>(silu, p, sm_count, st);
     if (Kp == 48) return launch_umma<3>(silu, p, sm_count, st);

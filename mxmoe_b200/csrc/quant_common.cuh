@@ -85,6 +85,49 @@ __device__ __forceinline__ uint2 quant8(const float (&v)[8], float sf, float rcp
   pk.y = __byte_perm(w[2], w[3], 0x6420);
   return pk;
 }
+// ---- the same 8 codes from PACKED fp16 values, entirely on the half2 pipe (no fp32 unpack, no Newton step in fp32).
+// q = RN16(x / s) is produced by Markstein's division in fp16 FMAs on operands normalised by a power of two:
+//   s' = s * 2^k in [1, 2),  x' = x * 2^k (exact),  r = RN16(1 / s'),
+//   q0 = RN16(x' r),  e = RN16(x' - q0 s')  (one FMA),  q1 = RN16(q0 + e r)  (one FMA)
+// Without the normalisation the residual e underflows for small scales and codes flip; with it, EVERY (x, s) pair with s a
+// normal fp16 number and |x / s| <= 160 gives the code of the reference arithmetic, rint(clamp(RN16(RN32(x / s)))), for both
+// the 8-bit and the 4-bit clamp — verified exhaustively (1.4e9 pairs, tools/verify_h2div.c).  Rows whose scale is an fp16
+// denormal (< 6.1e-5) take quant8.
+struct H2Div {
+  __half2 fac, r, sp;  // 2^k, RN16(1/s'), s' — each duplicated in both halves
+  bool fast;           // false: the scale is denormal, use quant8
+};
+__device__ __forceinline__ H2Div h2div_prepare(__half s) {
+  H2Div d;
+  const unsigned short sb = __half_as_ushort(s);
+  const int es = (sb >> 10) & 31;
+  d.fast = es != 0;
+  const unsigned short fac = es == 30 ? 0x0200u : static_cast<unsigned short>((30 - es) << 10);  // 2^(15 - es); 2^-15 is denormal
+  const unsigned short sp = static_cast<unsigned short>(0x3C00u | (sb & 0x3FFu));
+  const __half spv = __ushort_as_half(sp);
+  d.fac = __half2half2(__ushort_as_half(fac));
+  d.sp = __half2half2(spv);
+  d.r = __half2half2(__float2half_rn(__frcp_rn(__half2float(spv))));
+  return d;
+}
+__device__ __forceinline__ uint2 quant8_h2(const uint32_t (&hv)[4], const __half2 fac, const __half2 r, const __half2 sp, int upper) {
+  const __half2 hi2 = __float2half2_rn(static_cast<float>(upper)), lo2 = __float2half2_rn(static_cast<float>(-upper));
+  const __half2 magic = __float2half2_rn(1536.f);
+  uint32_t w[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const __half2 xp = __hmul2(*reinterpret_cast<const __half2*>(&hv[j]), fac);
+    const __half2 q0 = __hmul2(xp, r);
+    const __half2 e = __hfma2(__hneg2(q0), sp, xp);
+    __half2 q = __hfma2(e, r, q0);
+    q = __hadd2(__hmax2(__hmin2(q, hi2), lo2), magic);
+    w[j] = *reinterpret_cast<uint32_t*>(&q);
+  }
+  uint2 pk;
+  pk.x = __byte_perm(w[0], w[1], 0x6420);
+  pk.y = __byte_perm(w[2], w[3], 0x6420);
+  return pk;
+}
 // 8 quotients -> 8 E4M3 bytes (round to nearest even, saturating at +-448): the fp8 counterpart of quant8.  The E4M3
 // rounding boundaries are fp16-representable, so the argument above carries over: e4m3(q1) == e4m3(x / s) always.
 __device__ __forceinline__ uint2 quant8_e4m3(const float (&v)[8], float sf, float rcp) {

@@ -216,3 +216,49 @@ def test_repack_from_reference_layout(H, w_bits, a_bits, sym):
     got = H.repack_from_ref(dev(ref_packed), N, K, w_bits, a_bits, sym)
     torch.cuda.synchronize()
     assert np.array_equal(got.cpu().numpy(), want.reshape(N, -1))
+
+
+@pytest.mark.parametrize("n,rows,E", [(1408, 1000, 1), (5632, 333, 1), (2560, 517, 1), (1408, 2500, 5), (2816, 130, 3), (10240, 40, 1)])
+def test_hadamard_pipelined_kernel_bit_identical_to_phase_kernel(H, n, rows, E, monkeypatch):
+    """hadamard_pipe_kernel (warp-specialised: cp.async loaders / MMA issuer / TMEM drain + quantize from registers) against
+    hadamard_umma_kernel (MXB_HAD_PIPE=0: one phase at a time): the same arithmetic, so identical bits — int8 codes, scales
+    and fp16 pass-through rows, with mixed per-expert bit-widths (8 / 4 / 16), ragged row counts (partial last batch), row
+    gather, and both replication schemes in use (K = 176: 1408, 5632, 2816; K = 40: 2560; 10240 = 40 x 256 is NOT covered by
+    either and takes the long-row kernel on both sides)."""
+    rng = np.random.default_rng(n + rows)
+    x = rand16(rng, rows + 7, n, scale=2.0)
+    x[3, 7] = 40.0
+    src = rng.permutation(rows + 7)[:rows].astype(np.int32)
+    if E == 1:
+        offs, actq = None, [(8, -1)]
+    else:
+        cuts = np.sort(rng.integers(0, rows, E - 1))
+        offs = dev(np.concatenate([[0], cuts, [rows]]).astype(np.int32))
+        actq = [((8, 4, 16)[e % 3], -1) for e in range(E)]
+
+    def run():
+        return H.quant_act(dev(x), dev(src), rows, offs, actq, hadamard=True)
+    q8, f16, sc = run()
+    torch.cuda.synchronize()
+    monkeypatch.setenv("MXB_HAD_PIPE", "0")
+    q8b, f16b, scb = run()
+    torch.cuda.synchronize()
+    monkeypatch.delenv("MXB_HAD_PIPE")
+    o = np.concatenate([[0], cuts, [rows]]) if E > 1 else np.array([0, rows])
+    for e in range(E):
+        r0, r1 = int(o[e]), int(o[e + 1])
+        if actq[e][0] >= 16:
+            assert torch.equal(f16[r0:r1].view(torch.int16), f16b[r0:r1].view(torch.int16))
+        else:
+            assert torch.equal(q8[r0:r1], q8b[r0:r1])
+            assert torch.equal(sc[r0:r1].view(torch.int16), scb[r0:r1].view(torch.int16))
+    # and against the oracle, like the phase kernel is: dequantized rows within one quantization step
+    h = O.hadamard_f16(x[src])
+    e8 = [e for e in range(E) if actq[e][0] == 8]
+    if e8:
+        r0, r1 = int(o[e8[0]]), int(o[e8[0] + 1])
+        if r1 > r0:
+            rq, rs = O.quant_act(h[r0:r1], 8, -1)
+            deq = q8[r0:r1].cpu().numpy().astype(np.float32) * sc[r0:r1].cpu().numpy().astype(np.float32)
+            assert np.abs(deq - rq.astype(np.float32) * rs.astype(np.float32)).max() <= 1.01 * rs.astype(np.float32).max()
+            assert np.mean(q8[r0:r1].cpu().numpy().astype(np.int32) != rq) < 0.02

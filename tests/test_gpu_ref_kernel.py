@@ -5,6 +5,15 @@ What it pins, by EXECUTION of the reference's code rather than by restatement: t
 scale order `float(acc) * float(half(sa * sb))` with one rounding to fp16 (mm_tile.cuh:480-496, :636-648) and the
 packed operand layout of pack_wxax (quantize.cuh:424-475).  Integer kinds must agree bit for bit three ways
 (reference kernel == oracle == mxb_group_gemm); fp16 within 1e-3 of the output range (different fp32 summation order).
+
+A DEFECT of the reference found this way: GlobalTileC::load_scale (mm_tile.cuh:451-464) fetches the per-channel scales of
+an 8-column MMA block j at `j*8 + lane%4` and `+1`, while the accumulator fragment of that lane holds columns
+`j*8 + (lane%4)*2` and `+1` (its own write_frag_to_gmem, mm_tile.cuh:631).  Lanes with lane%4 != 0 therefore scale their
+columns with a NEIGHBOURING channel's scale.  The reference never notices (its quantized check path feeds raw fp16
+bytes, test.cu:518-519).  This library and the oracle apply scale_b[n] to column n, as the quantizer defines it
+(quant.py:40-106).  Both facts are tested: with scales that are constant inside every aligned 8-channel block the defect
+is invisible and the three implementations agree bit for bit; with general scales the reference kernel equals the
+oracle evaluated with the mis-indexed scale vector, bit for bit.
 Skipped when the reference kernel library was not built (no /root/reference at build time)."""
 import ctypes as C
 import os
@@ -42,12 +51,22 @@ def ptr_table(tensors):
     return torch.tensor([t.data_ptr() if t is not None else 0 for t in tensors], dtype=torch.int64, device="cuda")
 
 
-def build(rng, shapes):
-    """shapes: list of (M, N, K, bits).  Returns the operands in both layouts + oracle outputs."""
+def misindexed(sw):
+    """scale_b as the reference's load_scale applies it: column 8j + 2c + d gets the scale of channel 8j + c + d."""
+    n = np.arange(sw.shape[0])
+    j, c, d = n // 8, (n % 8) // 2, n % 2
+    return sw[8 * j + c + d]
+
+
+def build(rng, shapes, block_scales=True):
+    """shapes: list of (M, N, K, bits).  Returns the operands in both layouts + oracle outputs.
+    block_scales: every aligned block of 8 weight rows shares its absmax (hence its scale)."""
     items = []
     for (M, N, K, bits) in shapes:
         X = ((rng.random((M, K)) * 2 - 1)).astype(np.float16)
         W = ((rng.random((N, K)) * 2 - 1) * 0.25).astype(np.float16)
+        if block_scales:
+            W[:, 0] = (0.3 + 0.01 * (np.arange(N) // 8)).astype(np.float16)
         if bits == 16:
             items.append(dict(M=M, N=N, K=K, bits=16, A_ref=X, B_ref=W, A_nat=X, B_nat=W, sa=None, sb=None, ref=O.gemm_fp16(X, W)))
             continue
@@ -57,7 +76,8 @@ def build(rng, shapes):
                           A_ref=O.pack_wxax(qa, bits), B_ref=O.pack_wxax(qw, bits),          # the reference's packed halves
                           A_nat=qa.astype(np.int8), B_nat=O.pack_wxax_native(qw, bits),       # this library's native layouts
                           sa=np.ascontiguousarray(sa.reshape(M)), sb=np.ascontiguousarray(sw.reshape(N)),
-                          ref=O.gemm_wxax(qa, sa, qw, sw, -1)[1]))
+                          ref=O.gemm_wxax(qa, sa, qw, sw, -1)[1],
+                          ref_defect=O.gemm_wxax(qa, sa, qw, misindexed(sw.reshape(N)).reshape(N, 1), -1)[1]))
     return items
 
 
@@ -117,3 +137,20 @@ def test_reference_kernel_oracle_and_library_agree():
         else:
             assert np.array_equal(r.view(np.uint16), exp.view(np.uint16)), f"reference kernel != oracle (w{it['bits']}a{it['bits']})"
             assert np.array_equal(o.view(np.uint16), r.view(np.uint16)), f"mxb_group_gemm != reference kernel (w{it['bits']}a{it['bits']})"
+
+
+def test_reference_kernel_scale_indexing_defect_is_understood():
+    """General per-channel scales: the reference kernel's output is the oracle's with scale_b mis-indexed exactly as
+    load_scale does (bit for bit) — and differs from the correctly scaled result, which this library produces."""
+    lib = load_ref()
+    rng = np.random.default_rng(8)
+    items = build(rng, [(300, 384, 512, 8), (130, 256, 512, 4)], block_scales=False)
+    got_ref = run_reference(lib, items)
+    got_ours = run_ours(items)
+    for it, r, o in zip(items, got_ref, got_ours):
+        assert np.array_equal(r.view(np.uint16), it["ref_defect"].view(np.uint16))
+        assert np.array_equal(o.view(np.uint16), it["ref"].view(np.uint16))
+        assert not np.array_equal(r.view(np.uint16), it["ref"].view(np.uint16))
+        # columns whose lane has lane % 4 == 0 (columns 0, 1 of every 8) are unaffected
+        cols = np.arange(it["N"]) % 8 < 2
+        assert np.array_equal(r[:, cols].view(np.uint16), it["ref"][:, cols].view(np.uint16))
