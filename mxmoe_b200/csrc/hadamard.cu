@@ -14,6 +14,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "moe_ops.cuh"
@@ -64,6 +65,7 @@ struct HadParams {
   float scale;         // 1/sqrt(n)
   int warp_bytes;      // per-warp staging bytes
   int h_pitch;         // bytes per row of the shared copy of hmat
+  unsigned long long* trace;  // MXB_HAD_TRACE=1: globaltimer stamps of block 0's pipeline events (hadamard_pipe.inc), else null
   int dbg;             // MXB_HAD_DBG bit mask (profiling experiments only): 1 skip load-phase math, 2 skip MMA, 4 skip quant
 };
 
@@ -396,20 +398,43 @@ cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t
   p.scale = static_cast<float>(1.0 / sqrt(static_cast<double>(n)));
   p.h_pitch = Kp * 2 + 16;
   { const char* e = getenv("MXB_HAD_DBG"); p.dbg = e ? atoi(e) : 0; }
+  p.trace = nullptr;
+  static unsigned long long* trace_buf = nullptr;
+  const char* tr_env = getenv("MXB_HAD_TRACE");
+  const bool tracing = tr_env && atoi(tr_env) != 0;
+  if (tracing) {  // profiling aid: [role 0..3][event slot 0..255] nanosecond stamps of block 0, printed after the launch
+    if (!trace_buf) cudaMalloc(reinterpret_cast<void**>(&trace_buf), 4 * 256 * sizeof(unsigned long long));
+    cudaMemsetAsync(trace_buf, 0, 4 * 256 * sizeof(unsigned long long), st);
+    p.trace = trace_buf;
+  }
+  struct TraceDump {
+    bool on; cudaStream_t st; unsigned long long* buf;
+    ~TraceDump() {
+      if (!on) return;
+      static unsigned long long h[4 * 256];
+      cudaStreamSynchronize(st);
+      cudaMemcpy(h, buf, sizeof h, cudaMemcpyDeviceToHost);
+      unsigned long long t0 = ~0ull;
+      for (int i = 0; i < 4 * 256; ++i) if (h[i] && h[i] < t0) t0 = h[i];
+      const char* names[4] = {"producer(slot issued)", "loader0(slot full seen, slot done)", "mma(issued)", "drain0(t_full seen, barrier passed, stored)"};
+      for (int r = 0; r < 4; ++r) {
+        fprintf(stderr, "[had trace] %s:", names[r]);
+        for (int i = 0; i < 256 && h[r * 256 + i]; ++i) fprintf(stderr, " %.2f", (h[r * 256 + i] - t0) * 1e-3);
+        fprintf(stderr, "\n");
+      }
+    }
+  } trace_dump{tracing, st, trace_buf};
   static const int use_umma = [] { const char* e = getenv("MXB_HAD_UMMA"); return e ? atoi(e) : 1; }();
   // warp-specialised tcgen05 pipeline (hadamard_pipe.inc); MXB_HAD_PIPE=0 keeps the phase-by-phase kernel below (tests
   // compare the two bit for bit)
   const char* pipe_env = getenv("MXB_HAD_PIPE");
   const int use_pipe = pipe_env ? atoi(pipe_env) : 1;
   if (use_pipe && use_umma && !silu && K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {
-    if (Kp == 176) return launch_pipe<11>(p, sm_count, st);
-    if (Kp == 160) return launch_pipe<10>(p, sm_count, st);
-    if (Kp == 144) return launch_pipe<9>(p, sm_count, st);
-    if (Kp == 112) return launch_pipe<7>(p, sm_count, st);
-    if (Kp == 64) return launch_pipe<4>(p, sm_count, st);
-    if (Kp == 48) return launch_pipe<3>(p, sm_count, st);
-    if (Kp == 32) return launch_pipe<2>(p, sm_count, st);
-    if (Kp == 16) return launch_pipe<1>(p, sm_count, st);
+    cudaError_t perr = cudaSuccess;  // (a (K, m) the pipeline does not serve falls through to the phase kernel)
+#define MXB_TRY_PIPE(KT_) \
+    if (Kp == 16 * KT_ && launch_pipe<KT_>(p, sm_count, st, &perr)) return perr;
+    MXB_TRY_PIPE(11) MXB_TRY_PIPE(4) MXB_TRY_PIPE(3) MXB_TRY_PIPE(2) MXB_TRY_PIPE(1)
+#undef MXB_TRY_PIPE
   }
   if (use_umma && K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {  // tcgen05 form (hadamard_umma.inc)
     if (Kp == 176) return launch_umma<11>(silu, p, sm_count, st);

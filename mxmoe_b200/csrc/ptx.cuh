@@ -53,6 +53,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Non-blocking probe of a phase.  (mbarrier.try_wait is POTENTIALLY BLOCKING: on a phase that is not complete it suspends the
+// thread for a hardware time limit — measured ~4 us on B200 — which is fine inside a wait loop and ruinous inside a polling
+// loop that serves two queues.)
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, P;\n\t"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // try_wait with a suspend-time hint (ns): the thread may sleep in hardware until the phase completes or the hint expires,
 // instead of re-issuing the probe every few cycles (a warp that spins steals issue slots from its scheduler's other warps)
 __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
