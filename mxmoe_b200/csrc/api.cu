@@ -211,6 +211,7 @@ int build_dev_problem(mxb_context* c, const MxbProblem& p, int32_t* acc_out, boo
   if (p.c_row && !p.m_range) return fail(MXB_EINVAL, "c_row needs m_range (device-resident rows)");
   if (p.flags & ~(MXB_EPI_SILU_MUL | MXB_PRO_SILU_MUL)) return fail(MXB_EINVAL, "unknown problem flags 0x%x", p.flags);
   d->epi_flags = p.flags;
+  { static const int epi_vec = [] { const char* e = getenv("MXB_EPI_VEC"); return e ? atoi(e) : 0; }(); if (epi_vec) d->epi_flags |= 256; }  // measurement switch
   d->ldc = p.ldc > 0 ? p.ldc : ((p.flags & MXB_EPI_SILU_MUL) ? p.N / 2 : p.N);
   d->M = p.M;
   d->N = p.N;

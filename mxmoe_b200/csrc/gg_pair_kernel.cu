@@ -57,6 +57,7 @@ struct Smem {
   uint64_t* tmem_empty;  // [2] leader: epilogue warps of both CTAs drained the accumulator (16 arrivals)
   uint32_t* tmem_ptr;
   __half* sa_stage;      // [2][256] per-token scales of the tile being drained
+  uint8_t* c_stage;      // [2 groups][32 tokens][GP_CS_PITCH B]: output chunk transposed to token-major before it leaves
   int32_t* prefix;       // [P+1]
   int32_t* m_arr;        // [P]
   int32_t* row0;         // [P]
@@ -64,7 +65,9 @@ struct Smem {
 
 constexpr int GP_BAR_BYTES = 512;
 constexpr int GP_SA_BYTES = 2 * GP_BT * 2;
-constexpr int GP_SMEM_BYTES = 1024 + GP_STAGES * GP_STAGE_BYTES + GP_BAR_BYTES + GP_SA_BYTES + (3 * GG_MAXP + 4) * 4;
+constexpr int GP_CS_PITCH = 128 * 2 + 16;          // a token's 128 outputs of this CTA + 16 B: conflict-free 16-byte row reads
+constexpr int GP_CS_BYTES = 2 * 32 * GP_CS_PITCH;  // one 32-token chunk per epilogue group
+constexpr int GP_SMEM_BYTES = 1024 + GP_STAGES * GP_STAGE_BYTES + GP_BAR_BYTES + GP_SA_BYTES + GP_CS_BYTES + (3 * GG_MAXP + 4) * 4;
 
 __device__ __forceinline__ Smem carve(uint8_t* raw) {
   Smem s;
@@ -80,7 +83,8 @@ __device__ __forceinline__ Smem carve(uint8_t* raw) {
   s.tmem_empty = s.tmem_full + 2;
   s.tmem_ptr = reinterpret_cast<uint32_t*>(s.tmem_empty + 2);
   s.sa_stage = reinterpret_cast<__half*>(p + GP_BAR_BYTES);
-  s.prefix = reinterpret_cast<int32_t*>(p + GP_BAR_BYTES + GP_SA_BYTES);
+  s.c_stage = p + GP_BAR_BYTES + GP_SA_BYTES;
+  s.prefix = reinterpret_cast<int32_t*>(p + GP_BAR_BYTES + GP_SA_BYTES + GP_CS_BYTES);
   s.m_arr = s.prefix + GG_MAXP + 1;
   s.row0 = s.m_arr + GG_MAXP;
   return s;
@@ -327,7 +331,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       // the two-deep sa_stage buffer safe
       named_bar_sync(2, 256);
       __half* Cp = d.C + static_cast<int64_t>(crow0) * ldc + n;
+      // Vector form of the store (the normal case): the 4 warps of the group transpose a 32-token chunk through shared
+      // memory and every lane writes 16 bytes of a token's row (256 contiguous bytes per half warp, or 128 with the fused
+      // silu*mul) instead of 2 bytes at a 2*ldc stride: 8x fewer store instructions and full 128-byte lines — what a store
+      // into ANOTHER GPU's memory over NVLink needs (expert-parallel combine, MxbProblem.c_row).
       int32_t* ao = d.acc_out != nullptr ? d.acc_out + static_cast<int64_t>(t.t0) * N + n : nullptr;
+      const bool vec = (reinterpret_cast<uintptr_t>(d.C) & 15) == 0 && (ldc & 7) == 0 && ((silu ? (N >> 1) : N) & 7) == 0 && ao == nullptr;
+      const uint32_t cs = smem_u32(S.c_stage) + grp * (32 * GP_CS_PITCH);
+      const int ncol0 = t.n0 + int(rank) * 128;  // first weight row (output column) of this CTA's half of the tile
       mbar_wait(&S.tmem_full[acc], acc_phase);
       tc_fence_after();
       for (int c = grp * 32; c < t.nt; c += 64) {
@@ -369,6 +380,32 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
           // The pair swaps one value per two tokens; the even lane finishes token c+2j, the odd lane token c+2j+1, each
           // from the fp16-rounded gate/up the unfused GEMM would have stored (silu_mul_h: quant_common.cuh).
           const int odd = lane & 1;
+          if (vec) {
+            const uint32_t colb = cs + odd * GP_CS_PITCH + ((q * 32 + lane) >> 1) * 2;  // this pair's output column, rows c+odd, c+odd+2, ..
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+              const uint32_t send = odd ? ((h[j] & 0xFFFFu) | (h[j + 1] << 16)) : ((h[j] >> 16) | (h[j + 1] & 0xFFFF0000u));
+              const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, 1);
+#pragma unroll
+              for (int jj = 0; jj < 2; ++jj) {
+                const uint16_t own = odd ? static_cast<uint16_t>(h[j + jj] >> 16) : static_cast<uint16_t>(h[j + jj] & 0xFFFFu);
+                const uint16_t oth = static_cast<uint16_t>(jj ? (recv >> 16) : (recv & 0xFFFFu));
+                const __half g = __ushort_as_half(odd ? oth : own), u = __ushort_as_half(odd ? own : oth);
+                st_shared_b16(colb + 2 * (j + jj) * GP_CS_PITCH, __half_as_ushort(__float2half_rn(silu_mul_h(g, u))));
+              }
+            }
+            named_bar_sync(3 + grp, 128);
+            const int ntok = min(32, t.nt - c);
+            const int hcol = (ncol0 >> 1) + (lane & 7) * 8;  // 64 outputs of this CTA per token: 8 lanes x 16 bytes
+#pragma unroll
+            for (int it = 0; it < 2; ++it) {
+              const int row = q * 8 + it * 4 + (lane >> 3);
+              const uint4 val = ld_shared_v4(cs + row * GP_CS_PITCH + (lane & 7) * 16);
+              if (row < ntok && hcol < (N >> 1)) st_global_v4(d.C + static_cast<int64_t>(crow0 + c + row) * ldc + hcol, val);
+            }
+            named_bar_sync(3 + grp, 128);  // the chunk buffer is rewritten by the group's next chunk
+            continue;
+          }
           __half* hp = d.C + static_cast<int64_t>(crow0 + c + odd) * ldc + (n >> 1);
 #pragma unroll
           for (int j = 0; j < 16; j += 2) {
@@ -384,6 +421,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
               hp += 2 * ldc;
             }
           }
+          continue;
+        }
+        if (vec) {
+          const uint32_t colb = cs + (q * 32 + lane) * 2;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            st_shared_b16(colb + (2 * j) * GP_CS_PITCH, static_cast<uint16_t>(h[j] & 0xFFFFu));
+            st_shared_b16(colb + (2 * j + 1) * GP_CS_PITCH, static_cast<uint16_t>(h[j] >> 16));
+          }
+          named_bar_sync(3 + grp, 128);
+          const int ntok = min(32, t.nt - c);
+          const int col = ncol0 + (lane & 15) * 8;  // 128 outputs of this CTA per token: 16 lanes x 16 bytes
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int row = q * 8 + it * 2 + (lane >> 4);
+            const uint4 val = ld_shared_v4(cs + row * GP_CS_PITCH + (lane & 15) * 16);
+            if (row < ntok && col < N) st_global_v4(d.C + static_cast<int64_t>(crow0 + c + row) * ldc + col, val);
+          }
+          named_bar_sync(3 + grp, 128);  // the chunk buffer is rewritten by the group's next chunk
           continue;
         }
         __half* cp = Cp + static_cast<int64_t>(c) * ldc;
