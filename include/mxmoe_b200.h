@@ -183,6 +183,21 @@ int mxb_repack_act_from_ref(mxb_handle_t h, const void* ref_packed, int64_t M, i
  * (source token of every sorted slot, stable in (token, j) order); slot_of int32 [T,k] (sorted slot of (t,j)). */
 int mxb_permute(mxb_handle_t h, const int32_t* topk_ids, int T, int k, int E, int32_t* expert_offsets,
                 int32_t* src_row, int32_t* slot_of, void* stream);
+/* mxb_permute without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Needs no handle: `device` is made current, inputs and outputs are the caller's.  The block-histogram scratch that
+ * mxb_permute keeps in the handle's cudaMalloc'ed workspace lives in a file-scope __device__ array of
+ * MXB_PERMUTE_STATIC_BYTES (256 KiB, held by every GPU that loads the library until exit); its address is looked up with
+ * cudaGetSymbolAddress on the first call per device (make that call — T = 0 is enough — before a capture starts).  The call
+ * performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ * Limit: 4 * (1 + ceil(T*k / 2048) * E) <= MXB_PERMUTE_STATIC_BYTES (e.g. E = 64: T*k up to 2 095 104 rows), else
+ * MXB_EINVAL with the numbers in mxb_last_error(); device < 64.
+ * Every call on a device shares the one array, which keeps the previous call's contents (the call clears the ticket word
+ * it needs at zero; the histograms are rewritten): calls that OVERLAP on the GPU — different streams without an ordering
+ * between them — race.  Calls on one stream, or ordered by events, are safe.  Results are identical to mxb_permute's. */
+#define MXB_PERMUTE_STATIC_BYTES (256 * 1024)
+int mxb_permute_static(int device, const int32_t* topk_ids, int T, int k, int E, int32_t* expert_offsets,
+                       int32_t* src_row, int32_t* slot_of, void* stream);
 
 /* ---- piece (2): per-token activation quantization (+ optional Hadamard) ---- */
 /* x fp16 [T,H] gathered through src_row (NULL = identity, rows = n_rows) into sorted order; expert e owns

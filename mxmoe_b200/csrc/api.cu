@@ -845,6 +845,24 @@ int mxb_permute(mxb_handle_t c, const int32_t* topk_ids, int T, int k, int E, in
   return MXB_OK;
 }
 
+// No allocation, no handle: the scratch is moe_ops.cu's file-scope device array (see include/mxmoe_b200.h).
+int mxb_permute_static(int device, const int32_t* topk_ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
+                       int32_t* slot_of, void* stream) {
+  if (device < 0 || device >= 64) return fail(MXB_EINVAL, "mxb_permute_static: device %d outside [0, 64)", device);
+  if (T < 0 || k < 1 || E < 1 || E > 1024) return fail(MXB_EINVAL, "bad permute shape T=%d k=%d E=%d (E <= 1024)", T, k, E);
+  if (!expert_offsets || (T > 0 && (!topk_ids || !src_row || !slot_of))) return fail(MXB_EINVAL, "null pointer");
+  if (int64_t(T) * k > (int64_t(1) << 30)) return fail(MXB_EINVAL, "mxb_permute_static: T*k = %lld too large", (long long)(int64_t(T) * k));
+  static_assert(MXB_PERMUTE_STATIC_BYTES == 256 * 1024, "header and moe_ops.cu disagree");
+  if (mxb::permute_static_capacity() != size_t(MXB_PERMUTE_STATIC_BYTES)) return fail(MXB_EINVAL, "static scratch size mismatch");
+  const size_t need = mxb::permute_ws_bytes(T * k, E);
+  if (need > mxb::permute_static_capacity())
+    return fail(MXB_EINVAL, "mxb_permute_static: T*k=%d, E=%d needs %zu bytes of scratch, the static array holds %zu (use mxb_permute)",
+                T * k, E, need, mxb::permute_static_capacity());
+  CU_OK(cudaSetDevice(device));
+  CU_OK(mxb::permute_static_launch(device, topk_ids, T, k, E, expert_offsets, src_row, slot_of, static_cast<cudaStream_t>(stream)));
+  return MXB_OK;
+}
+
 int mxb_quant_act(mxb_handle_t c, const void* x, int H, const int32_t* src_row, int n_rows, const int32_t* expert_offsets,
                   const MxbActQ* actq, int E, int hadamard, void* out_q8, void* out_f16, void* scales, int scale_cols,
                   void* stream) {

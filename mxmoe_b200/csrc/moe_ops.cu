@@ -13,6 +13,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "moe_ops.cuh"
 #include "quant_common.cuh"
 
@@ -219,6 +221,46 @@ cudaError_t permute_launch(const int32_t* ids, int T, int k, int E, int32_t* exp
   permute_scatter_kernel<<<nblk, PERM_THREADS, sizeof(int32_t) * 9 * E, st>>>(ids, n, k, E, ws, expert_offsets, src_row,
                                                                               slot_of);
   return cudaGetLastError();
+}
+
+// ---- permute without any allocation (mxb_permute_static; no counterpart in the reference) -------------------------------
+// The same kernels, with the block-histogram scratch in a file-scope device array instead of the handle's cudaMalloc'ed
+// workspace.  PERM_STATIC_INTS * 4 = 256 KiB per GPU that loads the library, held until exit.  In HOST code the array's
+// name is only a stand-in for the symbol, not a device address: the address is looked up once per device, with that
+// device current, and that pointer is what the kernels receive.
+namespace {
+constexpr int PERM_STATIC_INTS = 64 * 1024;
+static __device__ __align__(256) int32_t g_permute_scratch[PERM_STATIC_INTS];
+constexpr int PERM_STATIC_MAX_DEV = 64;
+int32_t* g_permute_scratch_addr[PERM_STATIC_MAX_DEV] = {};
+std::mutex g_permute_scratch_mu;
+}  // namespace
+
+size_t permute_static_capacity() { return sizeof(int32_t) * PERM_STATIC_INTS; }
+
+// `device` must be the current device.  Every call on a device shares the one array: calls that overlap on the GPU
+// (different streams, no ordering between them) race on the ticket and the block histograms.
+cudaError_t permute_static_launch(int device, const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
+                                  int32_t* slot_of, cudaStream_t st) {
+  if (device < 0 || device >= PERM_STATIC_MAX_DEV) return cudaErrorInvalidDevice;
+  if (permute_ws_bytes(T * k, E) > permute_static_capacity()) return cudaErrorInvalidValue;
+  int32_t* ws = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_permute_scratch_mu);
+    ws = g_permute_scratch_addr[device];
+    if (!ws) {
+      const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ws), g_permute_scratch);
+      if (e != cudaSuccess) return e;
+      g_permute_scratch_addr[device] = ws;
+    }
+  }
+  // the array keeps the previous call's contents: the histograms are fully rewritten by permute_hist_kernel, the
+  // ticket ws[0] must start at zero (a call that was aborted mid-way would leave it armed)
+  if (T * k > PERM_CHUNK) {  // the two-kernel form is the one that uses the scratch
+    const cudaError_t e = cudaMemsetAsync(ws, 0, sizeof(int32_t), st);
+    if (e != cudaSuccess) return e;
+  }
+  return permute_launch(ids, T, k, E, expert_offsets, src_row, slot_of, ws, st);
 }
 
 // ============================================================================ per-token quantization

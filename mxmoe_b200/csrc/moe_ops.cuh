@@ -8,6 +8,10 @@ namespace mxb {
 size_t permute_ws_bytes(int n, int E);
 cudaError_t permute_launch(const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
                            int32_t* slot_of, int32_t* ws, cudaStream_t st);
+// the same launch with the scratch in a file-scope device array (no allocation; `device` must be current)
+size_t permute_static_capacity();
+cudaError_t permute_static_launch(int device, const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* src_row,
+                                  int32_t* slot_of, cudaStream_t st);
 
 // destination of one expert's rows in an expert-parallel dispatch (same layout as MxbRowDest, include/mxmoe_b200.h)
 struct RowDest {

@@ -74,6 +74,7 @@ EXPORTS = [
     ("mxb_set_ref_operands", _I, [_P, _I]),
     ("mxb_repack_act_from_ref", _I, [_P, _P, _I64, _I, _I, _P, _P]),
     ("mxb_permute", _I, [_P, _P, _I, _I, _I, _P, _P, _P, _P]),
+    ("mxb_permute_static", _I, [_I, _P, _I, _I, _I, _P, _P, _P, _P]),
     ("mxb_quant_act", _I, [_P, _P, _I, _P, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),
     ("mxb_silu_mul_quant", _I, [_P, _P, _I, _I, _P, C.POINTER(MxbActQ), _I, _I, _P, _P, _P, _I, _P]),
     ("mxb_ep_push_counts", _I, [_P, _P, _I, C.POINTER(_P), _I, _I, _P]),
@@ -119,6 +120,20 @@ def _ptr(t: Optional[torch.Tensor]):
 
 def _stream():
     return torch.cuda.current_stream().cuda_stream
+
+
+def permute_static(topk_ids: torch.Tensor, E: int, offs: torch.Tensor, src: torch.Tensor, slot: torch.Tensor):
+    """mxb_permute_static: the permute with its scratch in a file-scope device array (no handle, no allocation; at most
+    MXB_PERMUTE_STATIC_BYTES of block histograms, see include/mxmoe_b200.h).  Every argument is the caller's: topk_ids
+    int32 [T, k] contiguous, offs int32 [E+1], src int32 [>= T*k], slot int32 [T, k].  Calls that overlap on the GPU race."""
+    lib = load_library()
+    if topk_ids.dtype != torch.int32 or not topk_ids.is_contiguous() or not topk_ids.is_cuda:
+        raise MxbError("permute_static takes a contiguous int32 CUDA tensor (it does not convert: converting allocates)")
+    T, k = topk_ids.shape
+    rc = lib.mxb_permute_static(topk_ids.device.index, _ptr(topk_ids), T, k, E, _ptr(offs), _ptr(src), _ptr(slot), _stream())
+    if rc != 0:
+        raise MxbError(f"mxb_permute_static failed ({rc}): {lib.mxb_last_error().decode()}")
+    return offs, src, slot
 
 
 @dataclass

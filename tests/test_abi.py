@@ -27,7 +27,7 @@ def lib():
 
 def test_header_declares_expected_surface():
     syms = declared_symbols()
-    for s in ("mxb_create", "mxb_group_gemm", "mxb_group_gemm_reflayout", "mxb_permute", "mxb_quant_act",
+    for s in ("mxb_create", "mxb_group_gemm", "mxb_group_gemm_reflayout", "mxb_permute", "mxb_permute_static", "mxb_quant_act",
               "mxb_silu_mul_quant", "mxb_combine", "mxb_quant_pack_weight", "mxb_repack_from_ref", "mxb_select_tiles"):
         assert s in syms
 
