@@ -429,7 +429,11 @@ cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t
   // compare the two bit for bit)
   const char* pipe_env = getenv("MXB_HAD_PIPE");
   const int use_pipe = pipe_env ? atoi(pipe_env) : 1;
-  if (use_pipe && use_umma && !silu && K > 1 && p.m >= 8 && p.m <= 128 && !any_g128) {
+  // m = 256 / 512 (long rows: 14336 = 28 x 512, 20480 = 40 x 512, 7168 = 28 x 256) are served when K' <= 64
+  // (MXB_HAD_PIPE_WIDE=0 keeps hadamard_wide_kernel for them)
+  const char* pw_env = getenv("MXB_HAD_PIPE_WIDE");
+  const int m_max = (pw_env && atoi(pw_env) == 0) ? 128 : 512;
+  if (use_pipe && use_umma && !silu && K > 1 && p.m >= 8 && p.m <= m_max && !any_g128) {
     cudaError_t perr = cudaSuccess;  // (a (K, m) the pipeline does not serve falls through to the phase kernel)
 #define MXB_TRY_PIPE(KT_) \
     if (Kp == 16 * KT_ && launch_pipe<KT_>(p, sm_count, st, &perr)) return perr;

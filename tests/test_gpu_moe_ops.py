@@ -218,13 +218,16 @@ def test_repack_from_reference_layout(H, w_bits, a_bits, sym):
     assert np.array_equal(got.cpu().numpy(), want.reshape(N, -1))
 
 
-@pytest.mark.parametrize("n,rows,E", [(1408, 1000, 1), (5632, 333, 1), (2560, 517, 1), (1408, 2500, 5), (2816, 130, 3), (10240, 40, 1)])
+@pytest.mark.parametrize("n,rows,E", [(1408, 1000, 1), (5632, 333, 1), (2560, 517, 1), (1408, 2500, 5), (2816, 130, 3), (10240, 40, 1),
+                                      (20480, 700, 1), (14336, 450, 3), (7168, 500, 3), (10240, 333, 5)])
 def test_hadamard_pipelined_kernel_bit_identical_to_phase_kernel(H, n, rows, E, monkeypatch):
     """hadamard_pipe_kernel (warp-specialised: cp.async loaders / MMA issuer / TMEM drain + quantize from registers) against
     hadamard_umma_kernel (MXB_HAD_PIPE=0: one phase at a time): the same arithmetic, so identical bits — int8 codes, scales
     and fp16 pass-through rows, with mixed per-expert bit-widths (8 / 4 / 16), ragged row counts (partial last batch), row
-    gather, and both replication schemes in use (K = 176: 1408, 5632, 2816; K = 40: 2560; 10240 = 40 x 256 is NOT covered by
-    either and takes the long-row kernel on both sides)."""
+    gather, and both replication schemes in use (K = 176: 1408, 5632, 2816; K = 40: 2560).
+    Long rows (m = 256: 10240 = 40 x 256, 7168 = 28 x 256; m = 512 as two batches per row: 20480 = 40 x 512, 14336 = 28 x 512;
+    several rows per CTA so every barrier changes phase) run on the pipeline too; the other side is then hadamard_wide_kernel
+    (one CTA per row, mma.sync): the same butterfly order and fp16 staging, so the same bits are expected here as well."""
     rng = np.random.default_rng(n + rows)
     x = rand16(rng, rows + 7, n, scale=2.0)
     x[3, 7] = 40.0
