@@ -671,11 +671,17 @@ int actq_table(mxb_context* c, const MxbActQ* actq, int E, cudaStream_t st, cons
 #include "hadk_data.inc"
 
 // fp16 copy of the reference's K x K factor, zero padded to a multiple of 16, cached per K on the device
-int hadamard_matrix(mxb_context* c, int K, const void** dev, int* Kp_out) {
-  const int Kp = (K + 15) / 16 * 16;
+// A > 1: the Kronecker product hadK (x) H_A of order K * A (index (k, a) -> k * A + a, H_A the Sylvester matrix): a row of
+// K blocks of m is then K * A blocks of m / A, and the top log2(A) butterfly stages of the length-m transform happen inside
+// the tensor-core factor instead of on the CUDA cores (H_m = H_A (x) H_{m/A}).  Kp: padded order the kernels are built for.
+int hadamard_matrix(mxb_context* c, int K, int A, const void** dev, int* Kp_out) {
+  const int KA = K * A;
+  int Kp = (KA + 15) / 16 * 16;
+  if (A > 1 && Kp > 64) Kp = 176;  // the kernels exist for 16, 32, 48, 64 and 176
   *Kp_out = Kp;
+  const int key = K + 1000 * A;
   for (auto& h : c->hads)
-    if (h.first == K) {
+    if (h.first == key) {
       *dev = h.second;
       return MXB_OK;
     }
@@ -684,16 +690,17 @@ int hadamard_matrix(mxb_context* c, int K, const void** dev, int* Kp_out) {
     if (kHadTable[i].k == K) bits = kHadTable[i].bits;
   if (!bits) return fail(MXB_EINVAL, "no Hadamard matrix of order %d", K);
   std::vector<__half> h(size_t(Kp) * Kp, __float2half(0.f));
-  for (int i = 0; i < K; ++i)
-    for (int j = 0; j < K; ++j) {
-      const int b = i * K + j;
+  for (int i = 0; i < KA; ++i)
+    for (int j = 0; j < KA; ++j) {
+      const int b = (i / A) * K + (j / A);
       const int bit = (bits[b >> 3] >> (7 - (b & 7))) & 1;
-      h[size_t(i) * Kp + j] = __float2half(bit ? 1.f : -1.f);
+      const int sa = __builtin_popcount(unsigned((i % A) & (j % A))) & 1;  // H_A[a', a] = (-1)^popcount(a' & a)
+      h[size_t(i) * Kp + j] = __float2half((bit != 0) != (sa != 0) ? 1.f : -1.f);
     }
   void* d = nullptr;
   CU_OK(cudaMalloc(&d, h.size() * sizeof(__half)));
   CU_OK(cudaMemcpy(d, h.data(), h.size() * sizeof(__half), cudaMemcpyHostToDevice));
-  c->hads.emplace_back(K, d);
+  c->hads.emplace_back(key, d);
   *dev = d;
   return MXB_OK;
 }
@@ -719,17 +726,26 @@ int quant_common(mxb_context* c, bool silu, const void* x, int H, const int32_t*
     const int K = mxb::hadamard_factor(H);
     if (K == 0) return fail(MXB_EINVAL, "no Hadamard factorisation for row length %d (get_hadK would assert)", H);
     if (K > 1 && H / K < 8) return fail(MXB_EINVAL, "Hadamard row length %d = %d x %d: power-of-two part below 8 not supported", H, K, H / K);
-    const void* hmat = nullptr;
-    int Kp = 16;
-    if (K > 1) {
-      rc = hadamard_matrix(c, K, &hmat, &Kp);
-      if (rc) return rc;
-    }
     // group-wise and E4M3 quantization tails exist in the warp-per-row kernel only (quantize_row)
     bool generic = g128 != 0;
     for (int e = 0; e < E; ++e) generic = generic || actq[e].a_bits == MXB_BITS_E4M3;
+    // The butterfly stages over m run on the CUDA cores and are bound by the shuffle unit.  MXB_HAD_KRON=<cap> (opt-in) moves
+    // the top log2(A) of them into the tensor-core factor, hadK (x) H_A with K * A <= 176 and m / A >= 8 (2560 = 40 x 64 ->
+    // 160 x 16: 381 -> 231 us for 65536 rows).  It is the same transform but NOT the reference's rounding point: the
+    // reference rounds to fp16 after the whole length-m transform (fast_hadamard_transform returns fp16, then hadK @ in
+    // fp16, hadamard_utils.py:96-105), here the rounding would come log2(A) stages earlier, which moves about half of the
+    // outputs by one fp16 ulp.  Off by default: parity with the reference's staging comes first.
+    int A = 1;
+    const char* kron_env = getenv("MXB_HAD_KRON");
+    if (K > 1 && !generic && kron_env && atoi(kron_env) > 1) A = mxb::hadamard_split(H, K, atoi(kron_env));
+    const void* hmat = nullptr;
+    int Kp = 16;
+    if (K > 1) {
+      rc = hadamard_matrix(c, K, A, &hmat, &Kp);
+      if (rc) return rc;
+    }
     cudaError_t e = mxb::hadamard_quant_launch(silu, x, H, src_row, n_rows, expert_offsets, tab, E, out_q8, out_f16, scales,
-                                               scale_cols, hmat, K, Kp, c->sm_count, generic, st);
+                                               scale_cols, hmat, K * A, Kp, c->sm_count, generic, st);
     if (e != cudaSuccess) return fail(MXB_ECUDA, "hadamard_quant_launch: %s", cudaGetErrorString(e));
     return MXB_OK;
   }

@@ -373,6 +373,27 @@ int hadamard_factor(int n) {
   return (n & (n - 1)) == 0 ? 1 : 0;
 }
 
+// Largest power of two A <= cap such that the row, read as K * A blocks of m / A, is served by the pipelined kernel with at
+// least two staging slots (hadK (x) H_A as the tensor-core factor, api.cu hadamard_matrix); 1 keeps the reference's split.
+int hadamard_split(int n, int K, int cap) {
+  int best = 1;
+  for (int A = 2; A <= cap && K * A <= 176 && n / (K * A) >= 8; A *= 2) {
+    const int Kp = (K * A + 15) / 16 * 16;
+    HadParams p{};
+    p.n = n;
+    p.K = K * A;
+    p.m = n / (K * A);
+    int smem = 0, slots = 0;
+    if (Kp <= 16) slots = pipe_slots<1>(p, &smem);
+    else if (Kp <= 32) slots = pipe_slots<2>(p, &smem);
+    else if (Kp <= 48) slots = pipe_slots<3>(p, &smem);
+    else if (Kp <= 64) slots = pipe_slots<4>(p, &smem);
+    else slots = pipe_slots<11>(p, &smem);
+    if (slots >= 2 && p.m <= 128) best = A;
+  }
+  return best;
+}
+
 cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t* src_row, int n_rows,
                                   const int32_t* expert_offsets, const int32_t* actq_dev, int E, void* out_q8, void* out_f16,
                                   void* scales, int scale_cols, const void* hmat_dev, int K, int Kp, int sm_count,

@@ -31,6 +31,7 @@ cudaError_t ep_plan_launch(const int32_t* counts, int W, int rank, int E, void* 
                            void* const* peer_scales, int32_t* seg_offs, int32_t* back_row, RowDest* dest, cudaStream_t st);
 
 int hadamard_factor(int n);
+int hadamard_split(int n, int K, int cap);  // Kronecker widening of the tensor-core factor (hadamard.cu)
 cudaError_t hadamard_quant_launch(bool silu, const void* x, int n, const int32_t* src_row, int n_rows,
                                   const int32_t* expert_offsets, const int32_t* actq_dev, int E, void* out_q8, void* out_f16,
                                   void* scales, int scale_cols, const void* hmat_dev, int K, int Kp, int sm_count,

@@ -29,12 +29,28 @@ def route(router_logits: torch.Tensor, top_k: int, norm_topk_prob: bool) -> Tupl
     return ids.to(torch.int32).contiguous(), w.contiguous()
 
 
+def rotate_down_weight(handle: ops.Handle, W_down: torch.Tensor) -> torch.Tensor:
+    """The offline half of the online down-projection rotation (rotation.py:403-421: apply_exact_had_to_linear(W,
+    had_dim=-1, output=False) before the activation hook is installed): every row of W_down [H, I] — the in_features axis
+    — goes through the same Hadamard transform the activations get, so that (x Q)(W Q)^T = x W^T.  Runs on the device through
+    the library's own transform in fp16 pass-through mode (the reference rotates in float64 and casts back: the difference
+    is the fp16 staging of mxb_quant_act, an ulp of the rotated weight)."""
+    W = W_down.to(handle_device(handle), torch.float16).contiguous()
+    _, rot, _ = handle.quant_act(W, None, W.shape[0], None, [(16, -1)], hadamard=True)
+    return rot
+
+
+def handle_device(handle: ops.Handle) -> torch.device:
+    return torch.device("cuda", getattr(handle, "device", 0) or 0)
+
+
 class MxMoESparseBlock(torch.nn.Module):
     """forward(hidden_states [B, S, H] or [T, H]) -> (out, router_logits), like the HF sparse-MoE blocks.
 
     gate_weight: router [E, H]; shared_gate_weight: Qwen's shared_expert_gate [1, H] (None: shared expert, if any, is added
     ungated as in DeepSeek-V2).  `weights` / `qlayer` as for MoELayer: {e: (W_gate_up [2I', H], W_down [H, I'])} with index E
-    the (fused) shared expert, and the per-expert qconfig of the reference's JSON."""
+    the (fused) shared expert, and the per-expert qconfig of the reference's JSON.  With hadamard_down=True the W_down given
+    HERE must already be in the rotated basis (rotate_down_weight); from_dense_weights rotates plain HF weights itself."""
 
     def __init__(self, handle: ops.Handle, E: int, top_k: int, H: int, I: int, ns: int, qlayer: QLayerConfig, max_tokens: int,
                  gate_weight: torch.Tensor, weights: Optional[Dict[int, Tuple[torch.Tensor, torch.Tensor]]], norm_topk_prob: bool = False,
@@ -49,10 +65,16 @@ class MxMoESparseBlock(torch.nn.Module):
 
     @classmethod
     def from_dense_weights(cls, handle, qlayer, max_tokens, gate_weight, expert_weights, shared_weights=None, shared_gate_weight=None,
-                           top_k=2, norm_topk_prob=False, hadamard_down=False):
+                           top_k=2, norm_topk_prob=False, hadamard_down=False, weights_prerotated=False):
         """expert_weights: list of (gate_proj [I,H], up_proj [I,H], down_proj [H,I]) per routed expert — the parameters of an
         HF expert MLP; shared_weights: the same triple for the shared expert (intermediate ns*I).  gate and up are stacked
-        into the fused gate_up operand the GroupGEMM takes (gen_workload.py:70-76: N = 2I)."""
+        into the fused gate_up operand the GroupGEMM takes (gen_workload.py:70-76: N = 2I).  hadamard_down=True: every
+        down_proj is rotated first (rotate_down_weight) unless weights_prerotated says the caller already did — a
+        checkpoint written by the reference's rotation pass holds rotated weights."""
+        if hadamard_down and not weights_prerotated:
+            expert_weights = [(g, u, rotate_down_weight(handle, d)) for g, u, d in expert_weights]
+            if shared_weights is not None:
+                shared_weights = (shared_weights[0], shared_weights[1], rotate_down_weight(handle, shared_weights[2]))
         E = len(expert_weights)
         H = expert_weights[0][2].shape[0]
         I = expert_weights[0][0].shape[0]
