@@ -36,7 +36,10 @@ using namespace ptx;
 
 namespace {
 
-constexpr int GP_STAGES = 6;
+#ifndef GP_STAGES_N
+#define GP_STAGES_N 6
+#endif
+constexpr int GP_STAGES = GP_STAGES_N;  // (-DGP_STAGES_N=4/5: ring-depth sensitivity runs, tools/r02_ab.sh)
 constexpr int GP_THREADS = 512;  // 16 warps: TMA tokens, MMA, TMEM alloc, TMA weights, 4 epilogue, 4 converter, 4 epilogue
 constexpr int GP_W_BYTES = 128 * 128;  // this CTA's 128 weight rows x 128 B
 constexpr int GP_T_BYTES = 128 * 128;  // this CTA's half of the token tile, <= 128 rows x 128 B
@@ -120,6 +123,25 @@ struct PairWalk {
   }
 };
 
+#ifdef GP_TRACE
+// -DGP_TRACE builds only (tools/gg_trace.py): nanosecond stamps of the first cluster's leader CTA, [role][event]
+//   0 token producer: stage free seen      1 MMA: full seen   2 MMA: conv seen   3 MMA: k-block issued
+//   4 converter warp 8: packed slab landed  5 converter: arrived on conv
+//   6 epilogue warp 4: tmem_full seen (per tile)   7 epilogue: tile stored (per tile)   8 MMA: accumulator free seen (per tile)
+constexpr int GP_TR_N = 2048;
+__device__ unsigned long long gp_trace_buf[9][GP_TR_N];
+__device__ __forceinline__ void gp_tr(int role, int idx) {
+  if (blockIdx.x == 0 && (threadIdx.x & 31) == 0 && idx < GP_TR_N) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    gp_trace_buf[role][idx] = t;
+  }
+}
+#define GP_TR(role, idx) gp_tr(role, idx)
+#else
+#define GP_TR(role, idx) do {} while (0)
+#endif
+
 __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
@@ -195,6 +217,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
     const bool tokens = warp == 0;
     int stage = 0, desc_p = -1;
     uint32_t phase = 0;
+#ifdef GP_TRACE
+    int tr_kb = 0;
+#endif
     PairTile t;
     for (PairWalk w(S, P); w.next(&t);) {
       const DevProblem& d = probs[t.p];
@@ -205,7 +230,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       const int boxes = big ? 1 : (half + GP_TBOX_ROWS - 1) / GP_TBOX_ROWS;
       const uint32_t tok_bytes = big ? uint32_t(GP_T_BYTES) : uint32_t(boxes) * GP_TBOX_BYTES;
       const int trow = S.row0[t.p] + t.t0 + int(rank) * half;
+#ifdef GP_TOKM
+      // weights are the B operand: cta_group::2 takes the first N/2 rows of the tile from CTA 0 and the rest from CTA 1
+      const int wrow = t.n0 + int(rank) * (((min(GP_BN, d.N - t.n0) + 15) & ~15) >> 1);
+#else
       const int wrow = t.n0 + int(rank) * 128;
+#endif
       const int kblocks = d.kblocks, a_kstep = d.a_kstep, b_kstep = d.b_kstep;
       const bool has_conv = d.conv != CONV_NONE;
       // bytes counted on the leader's `full`: the token boxes of both CTAs (+ both weight halves when unconverted)
@@ -218,17 +248,28 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       }
       for (int kb = 0; kb < kblocks; ++kb) {
         mbar_wait(&S.empty[stage], phase ^ 1);
+#ifdef GP_TRACE
+        if (tokens) GP_TR(0, tr_kb++);
+#endif
         uint8_t* sw = S.stages + stage * GP_STAGE_BYTES;
         const uint32_t full_leader = mapa_u32(smem_u32(&S.full[stage]), 0);
         if (elect_one()) {
           if (tokens) {
+#ifdef GP_X_HALFTOK  // timing experiment (wrong results): token boxes only on even k-blocks
+            const bool skip_tok = (kb & 1) != 0;
+            if (leader) mbar_expect_tx(&S.full[stage], skip_tok ? tx_full - 2u * tok_bytes : tx_full);
+            if (skip_tok) { /* nothing to load */ } else
+#else
             if (leader) mbar_expect_tx(&S.full[stage], tx_full);
+#endif
+            {
             uint8_t* st = sw + GP_W_BYTES;
             if (big) {
               tma_load_2d_pair(st, tmT, full_leader, kb * a_kstep, trow);
             } else {
               for (int b = 0; b < boxes; ++b)
                 tma_load_2d_pair(st + b * GP_TBOX_BYTES, tmT, full_leader, kb * a_kstep, trow + b * GP_TBOX_ROWS);
+            }
             }
           } else if (has_conv) {
             mbar_expect_tx(&S.cfull[stage], GP_W_BYTES / 2);
@@ -248,43 +289,91 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       uint32_t phase = 0, conv_phase_bits = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      // Operand descriptors of the current stage as running values: a stage is 32 KB further, i.e. +2048 in the 14-bit
+      // address field (no carry out of it: the ring ends below 227 KB), so a k-block costs two adds instead of building both
+      // descriptors from the shared address (this lane's instruction count per k-block paces the tensor pipe).
+      const uint64_t da0 = umma_desc_sw128(smem_u32(S.stages)), db0 = umma_desc_sw128(smem_u32(S.stages) + GP_W_BYTES);
+      uint64_t da = da0, db = db0;
+#ifdef GP_TRACE
+      int tr_kb = 0, tr_tile = 0;
+#endif
       PairTile t;
       for (PairWalk w(S, P); w.next(&t);) {
         const DevProblem& d = probs[t.p];
         const int kblocks = d.kblocks;
+#ifdef GP_TOKM
+        // tokens on UMMA M (A operand, 128 rows of this tile's token chunk per CTA; rows past the chunk hold stale bytes whose
+        // products only reach accumulator lanes nobody reads), the tile's weight rows on UMMA N
+        const int ncols16 = (min(GP_BN, d.N - t.n0) + 15) & ~15;
+        const uint32_t idesc = d.idesc | ((uint32_t(ncols16) >> 3) << 17);
+#else
         const int nt16 = (t.nt + 15) & ~15;
         const uint32_t idesc = d.idesc | ((uint32_t(nt16) >> 3) << 17);
+#endif
         const bool is_i8 = d.mma_kind == MMA_I8, is_f8 = d.mma_kind == MMA_F8;
         const bool has_conv = d.conv != CONV_NONE;
+#ifdef GP_MMA_LANE0
+        if (lane != 0) continue;  // one lane runs the whole issue loop (no elect / reconvergence per k-block)
+#endif
         mbar_wait(&S.tmem_empty[acc], acc_phase ^ 1);
+#ifdef GP_TRACE
+        GP_TR(8, tr_tile++);
+#endif
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
         // The MMA kind is an opcode, not an operand: one copy of the k-block loop per kind, chosen once per tile.  (A kind
         // test per MMA inside the loop costs 4 % of the whole GEMM: this one lane's issue rate is the kernel's pace.)
         auto run_tile = [&](auto kind) {
           for (int kb = 0; kb < kblocks; ++kb) {
+#ifdef GP_CONV_FULL
+            if (!has_conv)
+#endif
             mbar_wait(&S.full[stage], phase);
+#ifdef GP_TRACE
+            GP_TR(1, tr_kb);
+#endif
             if (has_conv) {
               mbar_wait(&S.conv[stage], (conv_phase_bits >> stage) & 1);
               conv_phase_bits ^= 1u << stage;
             }
+#ifdef GP_TRACE
+            GP_TR(2, tr_kb);
+#endif
             tc_fence_after();
-            const uint32_t w_addr = smem_u32(S.stages + stage * GP_STAGE_BYTES);
-            const uint64_t da = umma_desc_sw128(w_addr);
-            const uint64_t db = umma_desc_sw128(w_addr + GP_W_BYTES);
+#ifdef GP_MMA_LANE0
+            {
+#else
             if (elect_one()) {
+#endif
+#ifdef GP_X_QUARTERMMA  // timing experiment (wrong results): one of the four MMAs of a k-block
+#define GP_KSTEPS 1
+#else
+#define GP_KSTEPS 4
+#endif
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
+              for (int k = 0; k < GP_KSTEPS; ++k) {
                 const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-                if constexpr (decltype(kind)::value == MMA_I8) umma_i8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
-                else if constexpr (decltype(kind)::value == MMA_F8) umma_f8_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
-                else umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accum);
+#ifdef GP_TOKM
+                const uint64_t ka = db + 2 * k, kb_ = da + 2 * k;  // A = token region, B = weight region
+#else
+                const uint64_t ka = da + 2 * k, kb_ = db + 2 * k;
+#endif
+                if constexpr (decltype(kind)::value == MMA_I8) umma_i8_pair(d_tmem, ka, kb_, idesc, accum);
+                else if constexpr (decltype(kind)::value == MMA_F8) umma_f8_pair(d_tmem, ka, kb_, idesc, accum);
+                else umma_f16_pair(d_tmem, ka, kb_, idesc, accum);
               }
               umma_commit_pair(&S.empty[stage], 3);
               if (kb == kblocks - 1) umma_commit_pair(&S.tmem_full[acc], 3);
             }
+#ifndef GP_MMA_LANE0
             __syncwarp();
-            if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
+#endif
+#ifdef GP_TRACE
+            GP_TR(3, tr_kb++);
+#endif
+            da += GP_STAGE_BYTES >> 4;
+            db += GP_STAGE_BYTES >> 4;
+            if (++stage == GP_STAGES) { stage = 0; phase ^= 1; da = da0; db = db0; }
           }
         };
         if (is_i8) run_tile(std::integral_constant<int, MMA_I8>{});
@@ -304,9 +393,109 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
     uint32_t acc_phase = 0;
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     const uint32_t tmem_empty_leader = mapa_u32(smem_u32(&S.tmem_empty[0]), 0);
+#ifdef GP_TRACE
+    int tr_tile = 0;
+#endif
     PairTile t;
     for (PairWalk w(S, P); w.next(&t);) {
       const DevProblem& d = probs[t.p];
+#ifdef GP_TOKM
+      // ---- token-major drain: TMEM lane = token (this CTA's half of the chunk), TMEM column = weight row of the tile.  A
+      // thread owns ONE output row and walks its columns 32 at a time: 64 contiguous bytes per chunk (32 with the fused
+      // silu*mul, whose (gate_i, up_i) pair sits in adjacent registers of the same thread), stored as 16-byte vectors.
+      const int N = d.N;
+      const int epi = d.epi;
+      const int shift = d.acc_shift;
+      const int64_t ldc = d.ldc;
+      const bool silu = (d.epi_flags & 1) != 0;
+      const bool facc = d.mma_kind == MMA_F8;
+      const int half_rows = ((t.nt + 15) & ~15) >> 1;   // token rows each CTA stages (producer: trow = ... + rank * half)
+      const int tok = q * 32 + lane;                    // row of this thread inside the CTA's half
+      const int trel = int(rank) * half_rows + tok;     // token inside the tile
+      const bool t_ok = tok < half_rows && trel < t.nt;
+      const int grow = S.row0[t.p] + t.t0 + trel;       // row of A (scale_a)
+      // C may start at another row than A (DevProblem::c_row): results written straight into a peer GPU's buffer
+      const int crow = (d.c_row != nullptr ? static_cast<int>(ld_nc_u32(d.c_row)) : S.row0[t.p]) + t.t0 + trel;
+      const int ncols = min(GP_BN, N - t.n0);           // weight rows (output columns) of this tile
+      __half* sb_buf = S.sa_stage + acc * GP_BT;        // the tile's per-channel scales (the buffer of the other orientation)
+      __half2 sa2 = __float2half2_rn(1.f);
+      if (epi == EPI_INT_ROWCOL) {
+        sb_buf[et] = et < ncols ? d.scale_b[t.n0 + et] : __float2half(0.f);
+        if (t_ok) sa2 = __half2half2(d.scale_a[static_cast<int64_t>(grow) * d.scale_a_ld]);
+      }
+      // every tile, also the unscaled ones: keeps the eight warps within one tile of each other (two-deep scale buffer)
+      named_bar_sync(2, 256);
+      int32_t* ao = d.acc_out != nullptr ? d.acc_out + static_cast<int64_t>(t.t0 + trel) * N + t.n0 : nullptr;
+      const bool vec = (reinterpret_cast<uintptr_t>(d.C) & 15) == 0 && (ldc & 7) == 0 && ((silu ? (N >> 1) : N) & 7) == 0;
+      __half* crowp = d.C + static_cast<int64_t>(crow) * ldc + (silu ? (t.n0 >> 1) : t.n0);
+      mbar_wait(&S.tmem_full[acc], acc_phase);
+#ifdef GP_TRACE
+      if (warp == 4) GP_TR(6, tr_tile);
+#endif
+      tc_fence_after();
+      for (int c = grp * 32; c < ncols; c += 64) {
+        uint32_t v[32];
+        tmem_ld_32x32(lane_addr + acc * 256 + c, v);
+        tmem_ld_wait();
+        const int valid = t_ok ? min(32, ncols - c) : 0;
+        uint32_t h[16];
+        if (epi == EPI_F32) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) h[j] = pack_half2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+        } else {
+          if (ao != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < valid) ao[c + j] = static_cast<int32_t>(v[j]) >> shift;
+          }
+          if (!facc) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__int2float_rn(static_cast<int32_t>(v[j]) >> shift));
+          }
+          const uint4* sbp = reinterpret_cast<const uint4*>(sb_buf + c);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const uint4 s4 = sbp[g];
+            const uint32_t sw[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const __half2 prod = __hmul2(sa2, *reinterpret_cast<const __half2*>(&sw[j]));
+              const float2 pf = __half22float2(prod);
+              h[g * 4 + j] = pack_half2(__uint_as_float(v[g * 8 + 2 * j]) * pf.x, __uint_as_float(v[g * 8 + 2 * j + 1]) * pf.y);
+            }
+          }
+        }
+        if (silu) {
+          // fused act_fn(gate) * up (MXB_EPI_SILU_MUL): columns (2i, 2i+1) of the tile are (gate_i, up_i), i.e. the two halves
+          // of h[i]: 16 outputs per chunk, from the fp16-rounded gate / up the unfused GEMM would have stored
+          uint32_t o[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const __half2 a = *reinterpret_cast<const __half2*>(&h[2 * j]), b = *reinterpret_cast<const __half2*>(&h[2 * j + 1]);
+            o[j] = pack_half2(silu_mul_h(__low2half(a), __high2half(a)), silu_mul_h(__low2half(b), __high2half(b)));
+          }
+          __half* op = crowp + (c >> 1);
+          if (vec && valid == 32) {
+            st_global_v4(op, make_uint4(o[0], o[1], o[2], o[3]));
+            st_global_v4(op + 8, make_uint4(o[4], o[5], o[6], o[7]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (2 * j + 1 < valid) st_global_b16(op + j, static_cast<uint16_t>(j & 1 ? o[j >> 1] >> 16 : o[j >> 1] & 0xFFFFu));
+          }
+          continue;
+        }
+        __half* op = crowp + c;
+        if (vec && valid == 32) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) st_global_v4(op + g * 8, make_uint4(h[4 * g], h[4 * g + 1], h[4 * g + 2], h[4 * g + 3]));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < valid) st_global_b16(op + j, static_cast<uint16_t>(j & 1 ? h[j >> 1] >> 16 : h[j >> 1] & 0xFFFFu));
+        }
+      }
+#else
       const int N = d.N;
       const int n = t.n0 + int(rank) * 128 + q * 32 + lane;  // this thread's output column (weight row)
       const bool n_ok = n < N;
@@ -336,12 +525,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       // silu*mul) instead of 2 bytes at a 2*ldc stride: 8x fewer store instructions and full 128-byte lines — what a store
       // into ANOTHER GPU's memory over NVLink needs (expert-parallel combine, MxbProblem.c_row).
       int32_t* ao = d.acc_out != nullptr ? d.acc_out + static_cast<int64_t>(t.t0) * N + n : nullptr;
-      const bool vec = (reinterpret_cast<uintptr_t>(d.C) & 15) == 0 && (ldc & 7) == 0 && ((silu ? (N >> 1) : N) & 7) == 0 && ao == nullptr;
+      // Only where it pays: a store into a PEER's memory (c_row) wants 16-byte rows; into local HBM the 2-byte stores below
+      // cost fewer instructions than the transpose (c2 GEMM pair 0.479 ms against 0.509 with the transpose everywhere), and
+      // issue slots are what this kernel runs out of.  MXB_EPI_VEC=1 (epi_flags bit 8) forces the transpose for measurements.
+      const bool vec = (d.c_row != nullptr || (d.epi_flags & 256) != 0) && (reinterpret_cast<uintptr_t>(d.C) & 15) == 0 && (ldc & 7) == 0 &&
+                       ((silu ? (N >> 1) : N) & 7) == 0 && ao == nullptr;
       const uint32_t cs = smem_u32(S.c_stage) + grp * (32 * GP_CS_PITCH);
       const int ncol0 = t.n0 + int(rank) * 128;  // first weight row (output column) of this CTA's half of the tile
       mbar_wait(&S.tmem_full[acc], acc_phase);
+#ifdef GP_TRACE
+      if (warp == 4) GP_TR(6, tr_tile);
+#endif
       tc_fence_after();
+#ifdef GP_X_NOEPI  // timing experiment (wrong results): the accumulator is handed back undrained
+      for (int c = t.nt; c < t.nt; c += 64) {
+#else
       for (int c = grp * 32; c < t.nt; c += 64) {
+#endif
         uint32_t v[32];
         tmem_ld_32x32(lane_addr + acc * 256 + c, v);
         tmem_ld_wait();
@@ -459,38 +659,66 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
           }
         }
       }
+#endif  // GP_TOKM
       tc_fence_before();
       __syncwarp();
+#ifdef GP_TRACE
+      if (warp == 4) GP_TR(7, tr_tile++);
+#endif
       if (lane == 0) mbar_arrive_cluster(tmem_empty_leader + acc * 8);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+#ifdef GP_CONV_W2
+  } else if (warp == 8 || warp == 2 || warp == 10 || warp == 11) {
+    // ============================================================ 4-bit weight converters (4 warps in EACH CTA): warp 2 (idle
+    // after the TMEM allocation) instead of warp 9, which shares its scheduler with the MMA issuer
+    const int ct = (warp == 2 ? 32 : (warp - 8) * 32) + lane;  // 0..127
+#else
   } else if (warp >= 8 && warp < 12) {
     // ============================================================ 4-bit weight converters (4 warps in EACH CTA)
     const int ct = threadIdx.x - 256;  // 0..127
+#endif
     int stage = 0;
     uint32_t cphase_bits = 0;
+#ifdef GP_CONV_FULL
+    int kbc = 0;  // k-blocks of every tile so far: full[stage] is in phase (kbc / GP_STAGES) & 1
+#endif
     const uint32_t conv_leader = mapa_u32(smem_u32(&S.conv[0]), 0);
+#ifdef GP_TRACE
+    int tr_kb = 0;
+#endif
     PairTile t;
     for (PairWalk w(S, P); w.next(&t);) {
       const DevProblem& d = probs[t.p];
       const int kblocks = d.kblocks;
       if (d.conv == CONV_NONE) {
         stage = (stage + kblocks) % GP_STAGES;
+#ifdef GP_CONV_FULL
+        kbc += kblocks;
+#endif
         continue;
       }
       for (int kb = 0; kb < kblocks; ++kb) {
         mbar_wait(&S.cfull[stage], (cphase_bits >> stage) & 1);
         cphase_bits ^= 1u << stage;
+#ifdef GP_TRACE
+        if (warp == 8) GP_TR(4, tr_kb);
+#endif
         uint8_t* wfin = S.stages + stage * GP_STAGE_BYTES;
         const uint8_t* wpk = wfin + GP_PACKED_OFF;
         // packed slab: 128 rows x 64 B; a 16-byte item holds 32 k (low nibbles k..k+15, high nibbles k+16..k+31).
         // Everything is read into registers before the first write: the expansion overwrites the packed bytes.
         uint4 w4[4];
+#ifdef GP_X_NOCONV  // timing experiment (wrong results): the slab is handed on unexpanded
+        (void)wpk; (void)wfin; (void)w4;
+        for (int j = 4; j < 4; ++j) {
+#else
 #pragma unroll
         for (int j = 0; j < 4; ++j) w4[j] = *reinterpret_cast<const uint4*>(wpk + (ct + j * 128) * 16);
         named_bar_sync(1, 128);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
+#endif
           const int i = ct + j * 128;
           const int row = i >> 2, c = i & 3;
           uint4 lo, hi;
@@ -503,8 +731,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
           *reinterpret_cast<uint4*>(wfin + row * 128 + (((2 * c + 1) ^ sw) << 4)) = hi;
         }
         fence_proxy_async_smem();
+#ifdef GP_CONV_FULL
+        // the leader's converters also wait for the tokens of both CTAs: `conv` complete then implies `full` complete and
+        // the MMA issuer — whose time per k-block paces the tensor pipe — waits on ONE barrier
+        if (leader) mbar_wait(&S.full[stage], (kbc / GP_STAGES) & 1);
+        ++kbc;
+#endif
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(conv_leader + stage * 8);
+#ifdef GP_TRACE
+        if (warp == 8) GP_TR(5, tr_kb++);
+#endif
         if (++stage == GP_STAGES) stage = 0;
       }
     }
@@ -532,3 +769,15 @@ void gg_pair_launch(const DevProblem* probs, int P, int grid, cudaStream_t strea
 }
 
 }  // namespace mxb
+
+#ifdef GP_TRACE
+extern "C" int mxb_debug_gp_trace(unsigned long long* out, int clear) {
+  using namespace mxb;
+  if (clear) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, gp_trace_buf) != cudaSuccess) return -1;
+    return int(cudaMemset(p, 0, sizeof(gp_trace_buf)));
+  }
+  return int(cudaMemcpyFromSymbol(out, gp_trace_buf, sizeof(gp_trace_buf)));
+}
+#endif
