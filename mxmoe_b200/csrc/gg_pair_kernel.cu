@@ -23,6 +23,12 @@
 //   * Epilogue: TMEM lane = weight row n, column = token.  The per-token scale is staged in smem, the
 //     per-channel scale lives in one register; the arithmetic (int32 -> float, times the fp16-rounded
 //     product sa*sb, one rounding to fp16) is the reference's, mm_tile.cuh:490,643.
+//   * Orientation is chosen PER TILE (tile_tokm): a token chunk of >= 160 rows over a full 256-row weight tile
+//     is computed the other way round — the same two smem regions with the operand descriptors swapped, tokens on
+//     UMMA M — so that a thread of the epilogue owns an output ROW: the per-token scale is a register, the
+//     per-channel scales are staged, gate/up pairs of the fused silu*mul sit in adjacent registers (no
+//     shuffles) and the chunk leaves as 16-byte vectors after a warp-private shared-memory transpose (8 rows x
+//     64 contiguous bytes per store instruction): a third of the weight-major drain's instructions, the same bits.
 //
 // Supported here: fp16, w8a8 and w4a4 with per-token / per-channel scales (g-1).  Lists containing
 // group-wise or weight-only problems run on gg_kernel.cu.
@@ -142,6 +148,26 @@ __device__ __forceinline__ void gp_tr(int role, int idx) {
 #define GP_TR(role, idx) do {} while (0)
 #endif
 
+// Orientation of a tile's accumulator: token-major — tokens on UMMA M, a thread drains one output ROW — for
+// (nearly) full token chunks over a full 256-row weight tile; weight-major (tokens on UMMA N, sized to the chunk) for the ragged
+// ones, where a 256-row M would waste tensor time on rows that do not exist.
+#ifdef GP_X_NOSTG  // timing experiment: everything but the global stores of the token-major drain (never-true extra condition)
+#define GP_X_STG_COND &&t.nt > 100000
+#else
+#define GP_X_STG_COND
+#endif
+// Measured (same box, c2 GEMM pair): 0.490 ms all weight-major, 0.479 ms with chunks of >= 160 tokens token-major (the extra
+// tensor time of a 256-row M over 192 tokens is free: the tensor pipe is not what this kernel waits for);
+// -DGP_TOKM_MIN=257 builds the all-weight-major kernel.
+#ifndef GP_TOKM_MIN
+#define GP_TOKM_MIN 160
+#endif
+__device__ __forceinline__ bool tile_tokm(const DevProblem& d, const PairTile& t) {
+  // (not into a peer GPU's buffer, c_row: there the weight-major drain's transposed 256-byte row segments suit NVLink better than
+  // 64-byte ones — expert-parallel c2 at 2 GPUs 0.868 ms against 0.894)
+  return t.nt >= GP_TOKM_MIN && d.N - t.n0 >= GP_BN && d.acc_out == nullptr && d.c_row == nullptr;
+}
+
 __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
@@ -209,7 +235,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
   tc_fence_after();
   const uint32_t tmem_base = *S.tmem_ptr;
 
-  if (warp == 0 || warp == 3) {
+#ifdef GP_MMA_W3  // the MMA issuer on scheduler 3, whose epilogue warps idle on token-major tiles of <= 192 tokens
+  constexpr int kMmaWarp = 3, kWeightTmaWarp = 1;
+#else
+  constexpr int kMmaWarp = 1, kWeightTmaWarp = 3;
+#endif
+  if (warp == 0 || warp == kWeightTmaWarp) {
     // ============================================================ TMA producers (in EACH CTA): warp 0 tokens, warp 3 weights.
     // The whole warp walks the tiles converged and one elected lane issues: with a single-thread region the compiler
     // wraps every UTMALDG in a uniform-register "waterfall" loop, and one thread issuing 5 loads per stage was the
@@ -230,12 +261,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       const int boxes = big ? 1 : (half + GP_TBOX_ROWS - 1) / GP_TBOX_ROWS;
       const uint32_t tok_bytes = big ? uint32_t(GP_T_BYTES) : uint32_t(boxes) * GP_TBOX_BYTES;
       const int trow = S.row0[t.p] + t.t0 + int(rank) * half;
-#ifdef GP_TOKM
-      // weights are the B operand: cta_group::2 takes the first N/2 rows of the tile from CTA 0 and the rest from CTA 1
-      const int wrow = t.n0 + int(rank) * (((min(GP_BN, d.N - t.n0) + 15) & ~15) >> 1);
-#else
       const int wrow = t.n0 + int(rank) * 128;
-#endif
       const int kblocks = d.kblocks, a_kstep = d.a_kstep, b_kstep = d.b_kstep;
       const bool has_conv = d.conv != CONV_NONE;
       // bytes counted on the leader's `full`: the token boxes of both CTAs (+ both weight halves when unconverted)
@@ -282,7 +308,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
         if (++stage == GP_STAGES) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // ============================================================ MMA issuer (leader CTA; warp converged, one elected lane issues)
     if (leader) {
       int stage = 0;
@@ -301,15 +327,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
       for (PairWalk w(S, P); w.next(&t);) {
         const DevProblem& d = probs[t.p];
         const int kblocks = d.kblocks;
-#ifdef GP_TOKM
-        // tokens on UMMA M (A operand, 128 rows of this tile's token chunk per CTA; rows past the chunk hold stale bytes whose
-        // products only reach accumulator lanes nobody reads), the tile's weight rows on UMMA N
-        const int ncols16 = (min(GP_BN, d.N - t.n0) + 15) & ~15;
-        const uint32_t idesc = d.idesc | ((uint32_t(ncols16) >> 3) << 17);
-#else
+        // token-major tile: tokens on UMMA M (A operand, 128 rows of the chunk per CTA; rows past the chunk hold stale bytes whose
+        // products only reach accumulator lanes nobody reads), the 256 weight rows on UMMA N
+        const bool tokm = tile_tokm(d, t);
         const int nt16 = (t.nt + 15) & ~15;
-        const uint32_t idesc = d.idesc | ((uint32_t(nt16) >> 3) << 17);
-#endif
+        const uint32_t idesc = d.idesc | ((uint32_t(tokm ? GP_BN : nt16) >> 3) << 17);
         const bool is_i8 = d.mma_kind == MMA_I8, is_f8 = d.mma_kind == MMA_F8;
         const bool has_conv = d.conv != CONV_NONE;
 #ifdef GP_MMA_LANE0
@@ -323,6 +345,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
         const uint32_t d_tmem = tmem_base + acc * 256;
         // The MMA kind is an opcode, not an operand: one copy of the k-block loop per kind, chosen once per tile.  (A kind
         // test per MMA inside the loop costs 4 % of the whole GEMM: this one lane's issue rate is the kernel's pace.)
+        const uint64_t dx = tokm ? db0 - da0 : 0;  // db - da is the same for every stage
         auto run_tile = [&](auto kind) {
           for (int kb = 0; kb < kblocks; ++kb) {
 #ifdef GP_CONV_FULL
@@ -353,11 +376,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
 #pragma unroll
               for (int k = 0; k < GP_KSTEPS; ++k) {
                 const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-#ifdef GP_TOKM
-                const uint64_t ka = db + 2 * k, kb_ = da + 2 * k;  // A = token region, B = weight region
-#else
-                const uint64_t ka = da + 2 * k, kb_ = db + 2 * k;
-#endif
+                const uint64_t ka = da + dx + 2 * k, kb_ = db - dx + 2 * k;  // token-major: A = token region, B = weight region
                 if constexpr (decltype(kind)::value == MMA_I8) umma_i8_pair(d_tmem, ka, kb_, idesc, accum);
                 else if constexpr (decltype(kind)::value == MMA_F8) umma_f8_pair(d_tmem, ka, kb_, idesc, accum);
                 else umma_f16_pair(d_tmem, ka, kb_, idesc, accum);
@@ -399,103 +418,125 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
     PairTile t;
     for (PairWalk w(S, P); w.next(&t);) {
       const DevProblem& d = probs[t.p];
-#ifdef GP_TOKM
-      // ---- token-major drain: TMEM lane = token (this CTA's half of the chunk), TMEM column = weight row of the tile.  A
-      // thread owns ONE output row and walks its columns 32 at a time: 64 contiguous bytes per chunk (32 with the fused
-      // silu*mul, whose (gate_i, up_i) pair sits in adjacent registers of the same thread), stored as 16-byte vectors.
-      const int N = d.N;
-      const int epi = d.epi;
-      const int shift = d.acc_shift;
-      const int64_t ldc = d.ldc;
-      const bool silu = (d.epi_flags & 1) != 0;
-      const bool facc = d.mma_kind == MMA_F8;
-      const int half_rows = ((t.nt + 15) & ~15) >> 1;   // token rows each CTA stages (producer: trow = ... + rank * half)
-      const int tok = q * 32 + lane;                    // row of this thread inside the CTA's half
-      const int trel = int(rank) * half_rows + tok;     // token inside the tile
-      const bool t_ok = tok < half_rows && trel < t.nt;
-      const int grow = S.row0[t.p] + t.t0 + trel;       // row of A (scale_a)
-      // C may start at another row than A (DevProblem::c_row): results written straight into a peer GPU's buffer
-      const int crow = (d.c_row != nullptr ? static_cast<int>(ld_nc_u32(d.c_row)) : S.row0[t.p]) + t.t0 + trel;
-      const int ncols = min(GP_BN, N - t.n0);           // weight rows (output columns) of this tile
-      __half* sb_buf = S.sa_stage + acc * GP_BT;        // the tile's per-channel scales (the buffer of the other orientation)
-      __half2 sa2 = __float2half2_rn(1.f);
-      if (epi == EPI_INT_ROWCOL) {
-        sb_buf[et] = et < ncols ? d.scale_b[t.n0 + et] : __float2half(0.f);
-        if (t_ok) sa2 = __half2half2(d.scale_a[static_cast<int64_t>(grow) * d.scale_a_ld]);
-      }
-      // every tile, also the unscaled ones: keeps the eight warps within one tile of each other (two-deep scale buffer)
-      named_bar_sync(2, 256);
-      int32_t* ao = d.acc_out != nullptr ? d.acc_out + static_cast<int64_t>(t.t0 + trel) * N + t.n0 : nullptr;
-      const bool vec = (reinterpret_cast<uintptr_t>(d.C) & 15) == 0 && (ldc & 7) == 0 && ((silu ? (N >> 1) : N) & 7) == 0;
-      __half* crowp = d.C + static_cast<int64_t>(crow) * ldc + (silu ? (t.n0 >> 1) : t.n0);
-      mbar_wait(&S.tmem_full[acc], acc_phase);
+      if (tile_tokm(d, t)) {
+        // ---- token-major drain: TMEM lane = token (this CTA's half of the chunk), TMEM column = weight row of the tile.  A
+        // thread owns ONE output row and walks its columns 32 at a time (64 contiguous bytes, 32 with the fused silu*mul, whose
+        // (gate_i, up_i) pair sits in adjacent registers of the same thread): a third of the weight-major drain's instructions.
+        // The warp then transposes the chunk through its private 2 KB of shared memory so that one store instruction writes
+        // 8 rows x 64 contiguous bytes (16 x 32 with silu) instead of 16 bytes in each of 32 rows.
+        const int N = d.N;
+        const int epi = d.epi;
+        const int shift = d.acc_shift;
+        const int64_t ldc = d.ldc;
+        const bool silu = (d.epi_flags & 1) != 0;
+        const bool facc = d.mma_kind == MMA_F8;
+        const int half_rows = ((t.nt + 15) & ~15) >> 1;   // token rows each CTA stages (producer: trow = ... + rank * half)
+        const int row_w0 = int(rank) * half_rows + q * 32;  // token (inside the tile) of this warp's lane 0
+        const int trel = row_w0 + lane;
+        const bool t_ok = q * 32 + lane < half_rows && trel < t.nt;
+        const int grow = S.row0[t.p] + t.t0 + trel;       // row of A (scale_a)
+        // C may start at another row than A (DevProblem::c_row): results written straight into a peer GPU's buffer
+        const int crow_w0 = (d.c_row != nullptr ? static_cast<int>(ld_nc_u32(d.c_row)) : S.row0[t.p]) + t.t0 + row_w0;
+        __half* sb_buf = S.sa_stage + acc * GP_BT;        // the tile's 256 per-channel scales (the buffer of the other orientation)
+        __half2 sa2 = __float2half2_rn(1.f);
+        if (epi == EPI_INT_ROWCOL) {
+          sb_buf[et] = d.scale_b[t.n0 + et];
+          if (t_ok) sa2 = __half2half2(d.scale_a[static_cast<int64_t>(grow) * d.scale_a_ld]);
+        }
+        named_bar_sync(2, 256);
+        const bool vec = (reinterpret_cast<uintptr_t>(d.C) & 15) == 0 && (ldc & 7) == 0 && ((silu ? (N >> 1) : N) & 7) == 0;
+        __half* cw0 = d.C + static_cast<int64_t>(crow_w0) * ldc + (silu ? (t.n0 >> 1) : t.n0);  // row of lane 0, first column of the tile
+        const uint32_t wb = smem_u32(S.c_stage) + (grp * 4 + q) * 2048;  // this warp's transpose buffer
+        mbar_wait(&S.tmem_full[acc], acc_phase);
 #ifdef GP_TRACE
-      if (warp == 4) GP_TR(6, tr_tile);
+        if (warp == 4) GP_TR(6, tr_tile);
 #endif
-      tc_fence_after();
-      for (int c = grp * 32; c < ncols; c += 64) {
-        uint32_t v[32];
-        tmem_ld_32x32(lane_addr + acc * 256 + c, v);
-        tmem_ld_wait();
-        const int valid = t_ok ? min(32, ncols - c) : 0;
-        uint32_t h[16];
-        if (epi == EPI_F32) {
+        tc_fence_after();
+#ifdef GP_X_NOEPI
+        for (int c = GP_BN; c < GP_BN; c += 64) {
+#else
+        // a warp whose 32 lanes lie past the chunk's rows (half_rows <= 96: the last quadrant) has nothing to drain
+        for (int c = q * 32 < half_rows ? grp * 32 : GP_BN; c < GP_BN; c += 64) {
+#endif
+          uint32_t v[32];
+          tmem_ld_32x32(lane_addr + acc * 256 + c, v);
+          tmem_ld_wait();
+#ifdef GP_X_LDONLY  // timing experiment: the accumulator is read and dropped (the test below is never true)
+          if (t.nt < 100000) continue;
+#endif
+          uint32_t h[16];
+          if (epi == EPI_F32) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) h[j] = pack_half2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-        } else {
-          if (ao != nullptr) {
+            for (int j = 0; j < 16; ++j) h[j] = pack_half2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+          } else {
+            if (!facc) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < valid) ao[c + j] = static_cast<int32_t>(v[j]) >> shift;
-          }
-          if (!facc) {
+              for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__int2float_rn(static_cast<int32_t>(v[j]) >> shift));
+            }
+            const uint4* sbp = reinterpret_cast<const uint4*>(sb_buf + c);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__int2float_rn(static_cast<int32_t>(v[j]) >> shift));
-          }
-          const uint4* sbp = reinterpret_cast<const uint4*>(sb_buf + c);
+            for (int g = 0; g < 4; ++g) {
+              const uint4 s4 = sbp[g];
+              const uint32_t sw[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const uint4 s4 = sbp[g];
-            const uint32_t sw[4] = {s4.x, s4.y, s4.z, s4.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const __half2 prod = __hmul2(sa2, *reinterpret_cast<const __half2*>(&sw[j]));
-              const float2 pf = __half22float2(prod);
-              h[g * 4 + j] = pack_half2(__uint_as_float(v[g * 8 + 2 * j]) * pf.x, __uint_as_float(v[g * 8 + 2 * j + 1]) * pf.y);
+              for (int j = 0; j < 4; ++j) {
+                const __half2 prod = __hmul2(sa2, *reinterpret_cast<const __half2*>(&sw[j]));
+                const float2 pf = __half22float2(prod);
+                h[g * 4 + j] = pack_half2(__uint_as_float(v[g * 8 + 2 * j]) * pf.x, __uint_as_float(v[g * 8 + 2 * j + 1]) * pf.y);
+              }
             }
           }
-        }
-        if (silu) {
-          // fused act_fn(gate) * up (MXB_EPI_SILU_MUL): columns (2i, 2i+1) of the tile are (gate_i, up_i), i.e. the two halves
-          // of h[i]: 16 outputs per chunk, from the fp16-rounded gate / up the unfused GEMM would have stored
-          uint32_t o[8];
+          if (silu) {
+            // fused act_fn(gate) * up (MXB_EPI_SILU_MUL): columns (2i, 2i+1) of the tile are (gate_i, up_i) = the two halves of
+            // h[i]: 16 outputs per chunk, from the fp16-rounded gate / up the unfused GEMM would have stored
+            uint32_t o[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const __half2 a = *reinterpret_cast<const __half2*>(&h[2 * j]), b = *reinterpret_cast<const __half2*>(&h[2 * j + 1]);
-            o[j] = pack_half2(silu_mul_h(__low2half(a), __high2half(a)), silu_mul_h(__low2half(b), __high2half(b)));
+            for (int j = 0; j < 8; ++j) {
+              const __half2 a = *reinterpret_cast<const __half2*>(&h[2 * j]), b = *reinterpret_cast<const __half2*>(&h[2 * j + 1]);
+              o[j] = pack_half2(silu_mul_h(__low2half(a), __high2half(a)), silu_mul_h(__low2half(b), __high2half(b)));
+            }
+            if (vec) {
+              // 32 rows x 32 B: piece p (16 B) of row r at r * 32 + ((p ^ (r >> 2 & 1)) << 4): conflict-free both ways
+              const uint32_t sx = static_cast<uint32_t>((lane >> 2) & 1) << 4;
+              st_shared_v4(wb + lane * 32 + sx, make_uint4(o[0], o[1], o[2], o[3]));
+              st_shared_v4(wb + lane * 32 + (sx ^ 16u), make_uint4(o[4], o[5], o[6], o[7]));
+              __syncwarp();
+#pragma unroll
+              for (int it = 0; it < 2; ++it) {
+                const int r = (lane >> 1) + 16 * it, pc = lane & 1;
+                const uint4 val = ld_shared_v4(wb + r * 32 + ((static_cast<uint32_t>(pc) ^ static_cast<uint32_t>((r >> 2) & 1)) << 4));
+                if (q * 32 + r < half_rows && row_w0 + r < t.nt GP_X_STG_COND)
+                  st_global_v4(cw0 + static_cast<int64_t>(r) * ldc + (c >> 1) + pc * 8, val);
+              }
+              __syncwarp();
+            } else if (t_ok) {
+              __half* op = cw0 + static_cast<int64_t>(lane) * ldc + (c >> 1);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) st_global_b16(op + j, static_cast<uint16_t>(j & 1 ? o[j >> 1] >> 16 : o[j >> 1] & 0xFFFFu));
+            }
+            continue;
           }
-          __half* op = crowp + (c >> 1);
-          if (vec && valid == 32) {
-            st_global_v4(op, make_uint4(o[0], o[1], o[2], o[3]));
-            st_global_v4(op + 8, make_uint4(o[4], o[5], o[6], o[7]));
-          } else {
+          if (vec) {
+            // 32 rows x 64 B: piece p of row r at r * 64 + ((p ^ (r >> 1 & 3)) << 4)
+            const uint32_t sx = static_cast<uint32_t>((lane >> 1) & 3);
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (2 * j + 1 < valid) st_global_b16(op + j, static_cast<uint16_t>(j & 1 ? o[j >> 1] >> 16 : o[j >> 1] & 0xFFFFu));
+            for (int pc = 0; pc < 4; ++pc)
+              st_shared_v4(wb + lane * 64 + ((static_cast<uint32_t>(pc) ^ sx) << 4), make_uint4(h[4 * pc], h[4 * pc + 1], h[4 * pc + 2], h[4 * pc + 3]));
+            __syncwarp();
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+              const int r = (lane >> 2) + 8 * it, pc = lane & 3;
+              const uint4 val = ld_shared_v4(wb + r * 64 + ((static_cast<uint32_t>(pc) ^ static_cast<uint32_t>((r >> 1) & 3)) << 4));
+              if (q * 32 + r < half_rows && row_w0 + r < t.nt GP_X_STG_COND) st_global_v4(cw0 + static_cast<int64_t>(r) * ldc + c + pc * 8, val);
+            }
+            __syncwarp();
+          } else if (t_ok) {
+            __half* op = cw0 + static_cast<int64_t>(lane) * ldc + c;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) st_global_b16(op + j, static_cast<uint16_t>(j & 1 ? h[j >> 1] >> 16 : h[j >> 1] & 0xFFFFu));
           }
-          continue;
         }
-        __half* op = crowp + c;
-        if (vec && valid == 32) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) st_global_v4(op + g * 8, make_uint4(h[4 * g], h[4 * g + 1], h[4 * g + 2], h[4 * g + 3]));
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < valid) st_global_b16(op + j, static_cast<uint16_t>(j & 1 ? h[j >> 1] >> 16 : h[j >> 1] & 0xFFFFu));
-        }
-      }
-#else
+      } else {
       const int N = d.N;
       const int n = t.n0 + int(rank) * 128 + q * 32 + lane;  // this thread's output column (weight row)
       const bool n_ok = n < N;
@@ -659,7 +700,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GP_THREADS, 1) gg_pa
           }
         }
       }
-#endif  // GP_TOKM
+      }  // weight-major drain
       tc_fence_before();
       __syncwarp();
 #ifdef GP_TRACE
