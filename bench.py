@@ -469,9 +469,9 @@ def main():
     else:
         ach = my_gemm_ops * steps / (ms_gemm * 1e-3) / 1e12
         # dram__bytes_read.sum + dram__bytes_write.sum of the two launches from one `ncu --set full` capture of this command
-        # (profiles/ncu_gg_pair_r01.txt: 315.2 + 138.3 MB gate_up, 212.9 + 148.8 MB down); only known for the default
+        # (profiles/ncu_gg_pair_r02.txt: 315.4 + 139.1 MB gate_up, 212.9 + 149.7 MB down); only known for the default
         # workload on one GPU
-        traffic = 815.2e6 if (args.workload == "c2" and W == 1 and not args.bs) else None
+        traffic = 817.1e6 if (args.workload == "c2" and W == 1 and not args.bs) else None
         issue_peak = {"int8": 4590.0, "f16": 2232.0}
         roof = {"bound": "tensor", "achieved": ach, "peak": int8_peak, "unit": "TOPS", "frac": ach / int8_peak, "traffic": traffic,
                 "kernel": ("gg_pair_kernel" if blocks[-1].fused_silu else "gg_persistent_kernel") +
@@ -523,7 +523,10 @@ def main():
 
 
 # sm__pipe_tensor_cycles_active (% of elapsed) of the GroupGEMM launches from the committed ncu captures of the default command
-NCU_TENSOR_PIPE = {"c2": {"gate_up": 0.54, "down": 0.57, "source": "profiles/ncu_gg_pair_r01.txt"}}
+# (round 2: token chunks of >= 160 rows run with UMMA M = 256 over the tokens, so this figure now includes the tensor time of
+# rows that do not exist — 192 of 256 for c2's routed experts; `achieved` counts algorithmic operations only)
+NCU_TENSOR_PIPE = {"c2": {"gate_up": 0.68, "down": 0.65, "source": "profiles/ncu_gg_pair_r02.txt",
+                          "note": "includes padded token rows of token-major tiles; round 1 (all weight-major): 0.54 / 0.57"}}
 
 
 if __name__ == "__main__":
