@@ -515,12 +515,22 @@ def main():
     if rank == 0:
         if not args.no_cpu and W == 1:
             line["cpu_baseline"] = run_cpu(wl, 3, 3)
+        if W == 1 and not args.bs and args.workload in GPU_REFERENCE:
+            line["gpu_reference"] = GPU_REFERENCE[args.workload]
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     if rc:
         sys.exit(rc)
 
+
+# The reference's OWN GroupGEMM kernel on the same B200 (its cta_gemm templates compiled for sm_100a, oracle/ref_gg_harness.cu),
+# measured by tools/ref_kernel_compare.py next to mxb_group_gemm on the same problem lists — a RECORD of that run: bench.py
+# itself never loads anything under oracle/ outside its CPU legs.
+GPU_REFERENCE = {"c2": {"unit": "TOPS", "gate_up": {"reference_kernel": 46.1, "mxb_group_gemm": 2384.0},
+                        "down": {"reference_kernel": 43.7, "mxb_group_gemm": 2197.4}, "speedup": 51,
+                        "kernel": "cta_gemm_multistage_v2 / _qab_v2, 128 x 128 tiles, mma.sync (s4 emulated on sm_100), grid = #SM",
+                        "source": "profiles/ref_kernel_compare_r02.jsonl (tools/ref_kernel_compare.py)"}}
 
 # sm__pipe_tensor_cycles_active (% of elapsed) of the GroupGEMM launches from the committed ncu captures of the default command
 # (round 2: token chunks of >= 160 rows run with UMMA M = 256 over the tokens, so this figure now includes the tensor time of
