@@ -26,6 +26,10 @@ def fake_quant_t(t: torch.Tensor, bits: int, gsize: int, sym: bool) -> torch.Ten
     """Quantizer.fake_quant (quant.py:40-106) on a torch tensor, clip = (1, 1)."""
     if bits >= 16:
         return t
+    if bits == O.BITS_E4M3:  # the FP8 kind (oracle.quant_e4m3): per-row scale absmax / 448, codes on torch's own float8_e4m3fn grid
+        scale = (t.abs().amax(dim=-1, keepdim=True) / O.E4M3_MAX).to(torch.float16).to(t.dtype)
+        scale = torch.where(scale == 0, torch.ones_like(scale), scale)
+        return (t / scale).clamp(-O.E4M3_MAX, O.E4M3_MAX).to(torch.float8_e4m3fn).to(t.dtype) * scale
     g = t.shape[-1] if gsize == -1 else gsize
     r = t.reshape(-1, g)
     if sym:

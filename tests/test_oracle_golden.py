@@ -160,3 +160,20 @@ def test_e4m3_qstr_roundtrip():
     assert q.qstr() == "w8a8_g-1_sym_E4M3"
     with pytest.raises(ValueError):
         QLinearConfig.from_qstr("w4a4_g-1_sym_E4M3")
+
+
+@pytest.mark.parametrize("bits,gsize,sym", [(8, -1, True), (4, -1, True), (4, 128, False), (8, 128, True), (-8, -1, True)])
+def test_cpu_arm_fake_quant_is_the_oracles(bits, gsize, sym):
+    """oracle/cpu_path.py (the torch code bench.py's CPU legs time) against oracle.fake_quant (pinned above against the
+    reference's Quantizer.fake_quant): identical values in fp16 arithmetic, for the integer grids and for the E4M3 kind
+    (bits = -8), so the timed baseline computes what the checker computes."""
+    import torch
+    from oracle import cpu_path as CP
+    rng = np.random.default_rng(5 + abs(bits))
+    x = (rng.standard_normal((48, 512)) * 0.7).astype(np.float16)
+    x[3] = 0  # all-zero row: the E4M3 kind guards scale == 0 like quant_weight (quantize.cuh:256); the int grids give NaN on both sides
+    got = CP.fake_quant_t(torch.from_numpy(x), bits, gsize, sym).numpy().astype(np.float32)
+    want = np.asarray(O.fake_quant(x, bits, gsize, sym), dtype=np.float32)
+    ok = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), ok)
+    assert np.array_equal(got[ok], want[ok])
