@@ -172,7 +172,9 @@ def test_cpu_arm_fake_quant_is_the_oracles(bits, gsize, sym):
     rng = np.random.default_rng(5 + abs(bits))
     x = (rng.standard_normal((48, 512)) * 0.7).astype(np.float16)
     x[3] = 0  # all-zero row: the E4M3 kind guards scale == 0 like quant_weight (quantize.cuh:256); the int grids give NaN on both sides
-    got = CP.fake_quant_t(torch.from_numpy(x), bits, gsize, sym).numpy().astype(np.float32)
+    # (the E4M3 kind is compared as the CPU arm runs it, on fp32 tensors: the oracle returns code * scale unrounded)
+    xt = torch.from_numpy(x).float() if bits < 0 else torch.from_numpy(x)
+    got = CP.fake_quant_t(xt, bits, gsize, sym).numpy().astype(np.float32)
     want = np.asarray(O.fake_quant(x, bits, gsize, sym), dtype=np.float32)
     ok = np.isfinite(want)
     assert np.array_equal(np.isfinite(got), ok)
